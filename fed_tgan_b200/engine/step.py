@@ -1,0 +1,303 @@
+"""The CTGAN local training step as an explicit op program (no autograd).
+
+Reference semantics: ``MDGANClient.train_model`` (``Server/dtds/distributed.py:328-417``),
+one discriminator update followed by one generator update per iteration:
+
+  D step   z, condvec, perm, real rows -> G(train-mode BN) -> apply_activate ->
+           D(fake), D(real) with independent dropout -> WGAN loss + slerp gradient penalty
+           (``ctgan.py:240-258``) -> Adam(D)
+  G step   z, condvec -> G -> apply_activate -> D(fake) -> -mean + cond_loss
+           (``ctgan.py:174-194``) -> Adam(G, weight_decay=l2scale)
+
+B200 design decisions (vs. the reference's autograd graph of ~300 tiny launches):
+
+* every buffer is preallocated once; ``torch.cat`` disappears because producers write
+  straight into column windows of wider buffers (``h = [r_L | ... | r_1 | z | c1]``,
+  ``X = [fake_cat ; real_cat ; interpolates]``);
+* fake, real and interpolated batches go through the discriminator as ONE 3*B/pack-row
+  batch;
+* the backward pass is closed form.  In particular the gradient-penalty double backward is
+  a short chain of GEMMs that re-uses the dropout/leaky masks of the interpolates'
+  forward pass (derivation in DESIGN.md), and the WGAN and penalty weight-gradients are
+  produced by the *same* GEMM by stacking their operands along K;
+* all randomness is counter-based and keyed by a device-resident step counter, so the
+  whole iteration is CUDA-graph capturable.
+
+The same program runs on CPU through ``ops.reference`` (that is what the tests compare
+against autograd) and on sm_100a through ``ops.native``.
+"""
+
+from __future__ import annotations
+
+import torch
+
+from .. import ops
+from ..config import CTGANConfig
+from ..features.layout import TableLayout
+from ..models.arena import DiscriminatorArena, GeneratorArena, round_up
+from .table import DeviceTable
+
+# random-stream ids (one per consumer inside an iteration)
+S_Z_D, S_COL_D, S_OPT_D, S_PERM, S_ROW, S_GUMBEL_D, S_ALPHA, S_DROP_D = range(8)
+S_Z_G, S_COL_G, S_OPT_G, S_GUMBEL_G, S_DROP_G = range(16, 21)
+
+
+class TrainEngine:
+    def __init__(self, cfg: CTGANConfig, layout: TableLayout, table: DeviceTable | None, device=None,
+                 g_arena: GeneratorArena | None = None, d_arena: DiscriminatorArena | None = None,
+                 seed: int | None = None):
+        self.cfg, self.layout, self.table = cfg, layout, table
+        self.device = torch.device(device if device is not None else (table.device if table else "cpu"))
+        dev = self.device
+        seed = cfg.seed if seed is None else seed
+        if layout.n_col == 0:
+            raise ValueError("table has no one-hot span: conditional sampling is undefined")
+        self.G = g_arena if g_arena is not None else GeneratorArena(cfg, layout, dev, seed=seed)
+        self.D = d_arena if d_arena is not None else DiscriminatorArena(cfg, layout, dev, seed=seed + 1)
+        self.rng = ops.RngState(seed, dev)
+        self.tables = layout.device_tables(dev)
+
+        B, P = cfg.batch_size, cfg.pack
+        Bp = B // P
+        E, dd, n_opt, n_col = cfg.embedding_dim, layout.data_dim, layout.n_opt, layout.n_col
+        self.B, self.Bp, self.E = B, Bp, E
+        f32 = dict(dtype=torch.float32, device=dev)
+        i32 = dict(dtype=torch.int32, device=dev)
+
+        # ---- generator side
+        self.gh = list(cfg.gen_dim)
+        self.sum_h = sum(self.gh)
+        self.d0 = E + n_opt
+        L = len(self.gh)
+        # off[l] = first column of r_l's window; off[0] = start of h0; layer l (1-based) reads
+        # columns [off[l-1]:] and writes [off[l]:off[l-1]]
+        self.off = [0] * (L + 1)
+        acc = 0
+        for l in range(L, 0, -1):
+            self.off[l] = acc
+            acc += self.gh[l - 1]
+        self.off[0] = acc
+        self.ld_h = round_up(self.sum_h + self.d0, 4)
+        self.ld_dd = round_up(dd, 4)
+        self.h = torch.zeros(B, self.ld_h, **f32)
+        self.a = [torch.zeros(B, hl, **f32) for hl in self.gh]
+        self.save_mean = [torch.zeros(hl, **f32) for hl in self.gh]
+        self.save_invstd = [torch.zeros(hl, **f32) for hl in self.gh]
+        self.fake = torch.zeros(B, self.ld_dd, **f32)
+        self.dfake = torch.zeros(B, self.ld_dd, **f32)
+        self.dh = torch.zeros(B, max(self.sum_h, 4), **f32)
+        self.da = [torch.zeros(B, hl, **f32) for hl in self.gh]
+        # ---- conditional vector / sampler state
+        self.col = torch.zeros(B, **i32)
+        self.opt = torch.zeros(B, **i32)
+        self.perm = torch.zeros(B, **i32)
+        self.rid = torch.zeros(B, **i32)
+        self.m1 = torch.zeros(B, n_col, **f32)
+        # ---- discriminator side
+        self.din = dd + n_opt
+        self.ld_din = self.D.ld_din
+        self.Din = P * self.ld_din
+        self.dhid = list(cfg.dis_dim)
+        self.X = torch.zeros(3 * B, self.ld_din, **f32)
+        self.Xp = self.X.view(3 * Bp, self.Din)
+        self.Lact = [torch.zeros(3 * Bp, hl, **f32) for hl in self.dhid]
+        self.Mask = [torch.zeros(3 * Bp, hl, **f32) for hl in self.dhid]
+        self.Z = [torch.zeros(3 * Bp, hl, **f32) for hl in self.dhid]
+        self.y = torch.zeros(3 * Bp, **f32)
+        self.dX = torch.zeros(B, self.ld_din, **f32)
+        self.dXp = self.dX.view(Bp, self.Din)
+        rs = torch.empty(3 * Bp, **f32)
+        rs[:Bp] = 1.0 / Bp
+        rs[Bp:2 * Bp] = -1.0 / Bp
+        rs[2 * Bp:] = 1.0
+        self.rowscale_d = rs
+        self.rowscale_g = torch.full((Bp,), -1.0 / Bp, **f32)
+        self.alpha = torch.zeros(B, **f32)
+        # ---- scalars (device resident; read back only on request)
+        self.loss_d = torch.zeros(1, **f32)
+        self.pen = torch.zeros(1, **f32)
+        self.loss_g_adv = torch.zeros(1, **f32)
+        self.ce = torch.zeros(1, **f32)
+        self.iterations = 0
+
+    # ------------------------------------------------------------------ helpers
+    def _gw(self, l):
+        return self.G.view(f"seq.{l}.fc.weight")
+
+    def _g(self, l, what):
+        return self.G.view(f"seq.{l}.{what}")
+
+    def _dw(self, l):
+        return self.D.view(f"{self.D.layer_keys[l]}.weight")
+
+    def _db(self, l):
+        return self.D.view(f"{self.D.layer_keys[l]}.bias")
+
+    def _rand(self, inject, key, shape):
+        if inject is not None and key in inject:
+            return inject[key]
+        return None
+
+    # ------------------------------------------------------------- sampling prep
+    def _prep(self, inject, prefix, with_real):
+        B, E = self.B, self.E
+        t = self.table
+        h0 = self.off[0]
+        rng = self.rng
+        R = lambda k: self._rand(inject, k, None)  # noqa: E731
+        ops.fill_normal(self.h[:, h0:h0 + E], z=R(f"z_{prefix}"), rng=rng, stream=S_Z_D if with_real else S_Z_G)
+        ops.sample_condvec(t.cum_p, self.tables["soft_width"], self.col, self.opt,
+                           u_col=R(f"u_col_{prefix}"), u_opt=R(f"u_opt_{prefix}"), rng=rng,
+                           stream=S_COL_D if with_real else S_COL_G)
+        c1 = self.h[:, h0 + E:h0 + E + self.layout.n_opt]
+        ops.write_condvec(self.col, self.opt, self.tables["soft_cstart"], c1, None if with_real else self.m1)
+        if with_real:
+            ops.argsort_perm(self.perm, u=R("u_perm"), rng=rng, stream=S_PERM)
+            ops.sample_rows(t.row_ptr, t.row_ids, self.tables["soft_cstart"], self.col, self.opt, self.rid,
+                            perm=self.perm, u=R("u_row"), rng=rng, stream=S_ROW)
+            real = self.X[B:2 * B]
+            ops.expand_rows(t.vals, t.codes, self.rid, self.tables, real)
+            dd = self.layout.data_dim
+            ops.write_condvec(self.col, self.opt, self.tables["soft_cstart"],
+                              real[:, dd:dd + self.layout.n_opt], None, self.perm)
+        return c1
+
+    # --------------------------------------------------------------- generator
+    def g_forward(self, training=True, h=None, a=None, fake=None):
+        h = self.h if h is None else h
+        a = self.a if a is None else a
+        fake = self.fake if fake is None else fake
+        L = len(self.gh)
+        for l in range(1, L + 1):
+            x = h[:, self.off[l - 1]: self.off[0] + self.d0]
+            ops.linear(x, self._gw(l - 1), a[l - 1], bias=self._g(l - 1, "fc.bias"))
+            ops.bn_relu_fwd(
+                a[l - 1], self._g(l - 1, "bn.weight"), self._g(l - 1, "bn.bias"),
+                self._g(l - 1, "bn.running_mean"), self._g(l - 1, "bn.running_var"),
+                h[:, self.off[l]: self.off[l - 1]],
+                self.save_mean[l - 1] if training else None, self.save_invstd[l - 1] if training else None,
+                training=training, eps=self.cfg.bn_eps, momentum=self.cfg.bn_momentum,
+                num_batches_tracked=self._g(l - 1, "bn.num_batches_tracked") if training else None,
+            )
+        ops.linear(h[:, : self.off[0] + self.d0], self.G.view(f"seq.{L}.weight"), fake[:, : self.layout.data_dim],
+                   bias=self.G.view(f"seq.{L}.bias"))
+        return fake
+
+    def g_backward(self):
+        """Given ``dfake`` (grad wrt pre-activation output), fill ``G.grad``."""
+        L = len(self.gh)
+        dd = self.layout.data_dim
+        dfake = self.dfake[:, :dd]
+        hfull = self.h[:, : self.off[0] + self.d0]
+        ops.linear(dfake, hfull, self.G.grad_view(f"seq.{L}.weight"), a_t=True, b_t=True)
+        ops.colsum(dfake, self.G.grad_view(f"seq.{L}.bias"))
+        dh = self.dh[:, : self.sum_h]
+        ops.linear(dfake, self.G.view(f"seq.{L}.weight")[:, : self.sum_h], dh, b_t=True)
+        for l in range(L, 0, -1):
+            lo, hi = self.off[l], self.off[l - 1]
+            ops.bn_relu_bwd(
+                dh[:, lo:hi], self.a[l - 1], self.save_mean[l - 1], self.save_invstd[l - 1],
+                self._g(l - 1, "bn.weight"), self._g(l - 1, "bn.bias"), self.da[l - 1],
+                self.G.grad_view(f"seq.{l - 1}.bn.weight"), self.G.grad_view(f"seq.{l - 1}.bn.bias"),
+            )
+            x = self.h[:, hi: self.off[0] + self.d0]
+            ops.linear(self.da[l - 1], x, self.G.grad_view(f"seq.{l - 1}.fc.weight"), a_t=True, b_t=True)
+            ops.colsum(self.da[l - 1], self.G.grad_view(f"seq.{l - 1}.fc.bias"))
+            if l > 1:
+                width = self.sum_h - hi      # columns of W_l that multiply r_{l-1}..r_1
+                ops.linear(self.da[l - 1], self._gw(l - 1)[:, :width], dh[:, hi: self.sum_h], b_t=True,
+                           accumulate=True)
+
+    # ------------------------------------------------------------ discriminator
+    def d_forward(self, rows, inject, key, stream):
+        """Forward rows ``[0:rows)`` of the packed batch; fills Lact/Mask/y."""
+        cfg = self.cfg
+        x = self.Xp[:rows]
+        for l, hl in enumerate(self.dhid):
+            u = None
+            if inject is not None and key in inject:
+                u = inject[key][l]
+            ops.linear(x, self._dw(l), self.Lact[l][:rows], bias=self._db(l), act="leaky_dropout",
+                       mask_out=self.Mask[l][:rows], u=u, rng=self.rng, stream=stream + l,
+                       slope=cfg.leaky_slope, p=cfg.dropout_p)
+            x = self.Lact[l][:rows]
+        nl = len(self.dhid)
+        ops.rowdot(x, self._dw(nl), self._db(nl), self.y[:rows])
+
+    def d_signals(self, rows, rowscale):
+        """Backward signals ``Z_l = dLoss/d(pre-activation_l)`` for ``loss = sum rowscale*y``."""
+        nl = len(self.dhid)
+        ops.scale_outer_mask(rowscale, self._dw(nl), self.Mask[nl - 1][:rows], self.Z[nl - 1][:rows])
+        for l in range(nl - 1, 0, -1):
+            ops.linear(self.Z[l][:rows], self._dw(l), self.Z[l - 1][:rows], b_t=True, mask_in=self.Mask[l - 1][:rows])
+
+    # ------------------------------------------------------------------- steps
+    def d_step(self, inject=None):
+        cfg, B, Bp = self.cfg, self.B, self.Bp
+        dd, n_opt, din = self.layout.data_dim, self.layout.n_opt, self.din
+        c1 = self._prep(inject, "d", with_real=True)
+        self.g_forward(training=True)
+        ops.activate_fwd(self.fake, self.tables, self.X[:B], tau=cfg.tau, u=self._rand(inject, "u_gumbel_d", None),
+                         rng=self.rng, stream=S_GUMBEL_D, cond=c1)
+        ops.slerp(self.X[B:2 * B, :din], self.X[:B, :din], self.X[2 * B:, :din],
+                  alpha=self._rand(inject, "alpha", None), rng=self.rng, stream=S_ALPHA)
+        self.d_forward(3 * Bp, inject, "u_drop_d", S_DROP_D)
+        # WGAN loss value
+        ops.colsum(self.y[:2 * Bp].view(-1, 1), self.loss_d, rowscale=self.rowscale_d[:2 * Bp])
+        # backward signals for all rows (interp rows carry the d y / d x seed)
+        self.d_signals(3 * Bp, self.rowscale_d)
+        nl = len(self.dhid)
+        I = slice(2 * Bp, 3 * Bp)
+        # input-gradient of the interpolates, penalty, and its gradient seed (in place)
+        ops.linear(self.Z[0][I], self._dw(0), self.Xp[I], b_t=True)
+        ops.gp_penalty(self.Xp[I], self.pen, lambda_=cfg.gp_lambda)
+        # tangent pass: F_l = (In_l @ V_l^T) * Mask_l, stored over the interp rows of Lact
+        src = self.Xp[I]
+        for l in range(nl):
+            ops.linear(src, self._dw(l), self.Lact[l][I], mask_in=self.Mask[l][I])
+            src = self.Lact[l][I]
+        # weight gradients: WGAN rows and penalty rows stacked along K
+        inp = self.Xp
+        for l in range(nl):
+            ops.linear(self.Z[l], inp, self.D.grad_view(f"{self.D.layer_keys[l]}.weight"), a_t=True, b_t=True)
+            ops.colsum(self.Z[l][:2 * Bp], self.D.grad_view(f"{self.D.layer_keys[l]}.bias"))
+            inp = self.Lact[l]
+        ops.colsum(self.Lact[nl - 1], self.D.grad_view(f"{self.D.layer_keys[nl]}.weight").view(-1),
+                   rowscale=self.rowscale_d)
+        # d loss_d / d b_head = sum(rowscale over fake+real) = 0 exactly: its grad slot stays 0
+        ops.adam_step(self.D.data[: self.D.n_trainable], self.D.grad, self.D.exp_avg, self.D.exp_avg_sq,
+                      self.rng.state[1:2], lr=cfg.lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.adam_eps)
+
+    def g_step(self, inject=None):
+        cfg, B, Bp = self.cfg, self.B, self.Bp
+        dd = self.layout.data_dim
+        c1 = self._prep(inject, "g", with_real=False)
+        self.g_forward(training=True)
+        ops.activate_fwd(self.fake, self.tables, self.X[:B], tau=cfg.tau, u=self._rand(inject, "u_gumbel_g", None),
+                         rng=self.rng, stream=S_GUMBEL_G, cond=c1)
+        self.d_forward(Bp, inject, "u_drop_g", S_DROP_G)
+        ops.colsum(self.y[:Bp].view(-1, 1), self.loss_g_adv, rowscale=self.rowscale_g)
+        self.d_signals(Bp, self.rowscale_g)
+        ops.linear(self.Z[0][:Bp], self._dw(0), self.dXp, b_t=True)
+        ops.activate_bwd(self.dX[:, :dd], self.X[:B, :dd], self.tables, self.dfake, tau=cfg.tau)
+        ops.cond_loss_fwd_bwd(self.fake, c1, self.m1, self.tables, self.dfake, self.ce, accumulate=True)
+        self.g_backward()
+        ops.adam_step(self.G.data[: self.G.n_trainable], self.G.grad, self.G.exp_avg, self.G.exp_avg_sq,
+                      self.rng.state[1:2], lr=cfg.lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.adam_eps,
+                      weight_decay=cfg.l2scale)
+
+    def iteration(self, inject=None):
+        self.rng.tick()
+        self.d_step(inject)
+        self.g_step(inject)
+        self.iterations += 1
+
+    def train(self, steps: int):
+        for _ in range(int(steps)):
+            self.iteration()
+
+    # ----------------------------------------------------------------- logging
+    def losses(self):
+        """Host copy of the last iteration's losses (synchronises)."""
+        ld, pen, adv, ce = (float(t.item()) for t in (self.loss_d, self.pen, self.loss_g_adv, self.ce))
+        return {"loss_d": ld, "pen": pen, "loss_g": adv + ce, "cond_loss": ce}
