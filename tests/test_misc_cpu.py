@@ -1,0 +1,152 @@
+import json
+import os
+
+import numpy as np
+import pandas as pd
+import torch
+
+from fed_tgan_b200.config import CTGANConfig
+from fed_tgan_b200.data import Date, FileGenerator, Transform, prepare_data
+from fed_tgan_b200.data.schemas import get_schema, make_table, split_table
+from fed_tgan_b200.features import (BGM_CTGAN_Transformer, DiscretizeTransformer, GeneralTransformer,
+                                     GMMTransformer, TableganTransformer, TableLayout)
+from fed_tgan_b200.models.synthesizer import CTGANSynthesizer
+from fed_tgan_b200.parallel import weights as W
+from fed_tgan_b200.parallel.client import MDGANClient
+from fed_tgan_b200.parallel.federator import MDGANServer
+from fed_tgan_b200.parallel.launcher import build_parser, federate
+
+
+def test_worked_weight_example():
+    """SURVEY 3.2 oracle: weights [0.40733, 0.59267]."""
+    rng = np.random.default_rng(0)
+    a, b = rng.normal(0, 1, 1000), rng.normal(2, 1, 3000)
+    j = W.categorical_similarity([[np.array([90.0, 10.0]), np.array([10.0, 90.0])]])
+    w = W.continuous_similarity([[a, b]])
+    assert np.allclose(j, 0.5)
+    assert np.allclose(W.final_weights(j, w, [1000, 3000]), [0.40733, 0.59267], atol=1e-4)
+
+
+def test_distances_match_scipy():
+    from scipy.spatial import distance
+    from scipy.stats import wasserstein_distance
+
+    rng = np.random.default_rng(1)
+    for _ in range(5):
+        p, q = rng.integers(0, 50, 9) + 1, rng.integers(0, 50, 9)
+        q[0] += 1
+        assert abs(W.jensenshannon(p, q) - distance.jensenshannon(p, q)) < 1e-12
+        u, v = rng.normal(size=300), rng.normal(1, 2, size=170)
+        assert abs(W.wasserstein_1d(u, v) - wasserstein_distance(u, v)) < 1e-10
+
+
+def test_zero_columns_rules():
+    same = [[np.array([5.0, 5.0]), np.array([10.0, 10.0])]]
+    assert np.allclose(W.categorical_similarity(same), 0.5)          # categorical: 1/N
+    s = np.arange(10.0)
+    assert np.allclose(W.continuous_similarity([[s, s]]), 0.0)       # continuous: stays 0
+
+
+def test_file_generator_semantics(tmp_path):
+    df = pd.DataFrame({"a": [0, 1, 2, 3], "b": ["x", "y", "x", " "], "c": [0.5, 1.5, 2.5, 3.5]})
+    meta = prepare_data("t_train.csv", ["a", "b", "c"], ["b"], ["a"], {}, "b", "", dataframe=df)
+    cols = meta["columns"]
+    assert cols[0]["type"] == "continous" and np.isclose(cols[0]["max"], np.log(4.0))
+    assert cols[1]["i2s"] == {"x": 2, "y": 1, "empty": 1} and meta["integer_info"] == ["a"]
+    assert meta["non_negative_cols"] == ["a"] and meta["target"] == "b"
+
+
+def test_transform_inverse_roundtrip():
+    from sklearn.preprocessing import LabelEncoder
+
+    meta = {"columns": [{"column_name": "a", "type": "continous"}, {"column_name": "b", "type": "categorical"}],
+            "date_info": {}, "non_negative_cols": ["a"], "name": "t"}
+    le = LabelEncoder().fit(["x", "y", "empty"])
+    data = np.array([[np.log(4.0), le.transform(["x"])[0]], [np.log(1.0), le.transform(["empty"])[0]]])
+    df, _, names = Transform.inverse(data, meta, [{"column_name": "b", "label_encoder": le}])
+    assert names == ["a", "b"] and np.allclose(df["a"].astype(float), [3.0, 0.0]) and list(df["b"]) == ["x", " "]
+
+
+def test_date_roundtrip():
+    df = pd.DataFrame({"d": ["2021-03-05", "2020-12-31"], "v": [1.0, 2.0]})
+    cats = ["d"]
+    out = Date.convert(df.copy(), {"d": "YYYY-MM-DD"}, cats)
+    assert {"d-year", "d-month", "d-day"} <= set(out.columns) and "d" not in out.columns
+    assert cats == ["d-year", "d-month", "d-day"]
+    back = Date.inverse_transform(out, {"d": "YYYY-MM-DD"})
+    assert "d" in back.columns and pd.Timestamp(back["d"][0]).month == 3
+
+
+def test_other_transformers_roundtrip():
+    rng = np.random.default_rng(0)
+    data = np.stack([rng.normal(size=200), rng.integers(0, 3, 200).astype(float)], 1)
+    g = GeneralTransformer("tanh"); g.fit(data, (1,)); assert np.allclose(g.inverse_transform(g.transform(data)), data, atol=1e-6)
+    d = DiscretizeTransformer(5); d.fit(data, (1,)); assert d.transform(data.copy())[:, 0].max() <= 4
+    t = TableganTransformer(2); t.fit(data, (1,)); assert np.allclose(t.inverse_transform(t.transform(data)), data, atol=1e-3)
+    m = GMMTransformer(3); m.fit(data, (1,)); enc = m.transform(data); assert enc.shape[1] == 1 + 3 + 3
+    assert np.array_equal(m.inverse_transform(enc, None)[:, 1], data[:, 1])
+
+
+def test_vb_backend_compact_roundtrip():
+    rng = np.random.default_rng(0)
+    n = 1500
+    data = np.stack([np.concatenate([rng.normal(0, 1, n // 2), rng.normal(9, 0.5, n // 2)]),
+                     rng.integers(0, 4, n).astype(float)], 1)
+    t = BGM_CTGAN_Transformer(backend="vb", seed=0)
+    t.fit(data, (1,))
+    vals, codes = t.transform_compact(data)
+    dense = t.expand(vals, codes)
+    assert dense.shape[1] == t.output_dim and isinstance(t.layout, TableLayout)
+    rt = t.inverse_transform(dense)
+    assert np.array_equal(rt[:, 1], data[:, 1])
+    inside = np.abs(vals[:, 0]) < 0.99
+    assert np.abs(rt[inside, 0] - data[inside, 0]).max() < 1e-4
+
+
+def test_cli_flags():
+    a = build_parser().parse_args(["-epoch", "7", "-rank", "0", "-categorical_list", "a,b", "-date_dic", '{"d":"YYYY-MM-DD"}'])
+    assert a.epochs == 7 and a.categorical_list == ["a", "b"] and a.date_dic == {"d": "YYYY-MM-DD"}
+    assert build_parser().parse_args(["-epochs", "3"]).epochs == 3
+    d = build_parser().parse_args([])
+    assert d.port == 7788 and d.world_size == 2 and d.target_column == "class" and len(d.selected_variables) == 42
+
+
+def test_standalone_synthesizer():
+    schema = get_schema("adult", rows=400)
+    df = make_table(schema, seed=0)
+    enc = df.copy()
+    for c in schema.categorical:
+        enc[c] = pd.factorize(df[c])[0]
+    s = CTGANSynthesizer(embedding_dim=8, gen_dim=(16,), dis_dim=(16,), batch_size=50, epochs=1, device="cpu",
+                         vgm_backend="vb", verbose=False)
+    s.fit(enc.to_numpy(float), [df.columns.get_loc(c) for c in schema.categorical])
+    out = s.sample(120)
+    assert out.shape == (120, len(schema.columns)) and np.isfinite(out).all()
+
+
+def test_checkpoint_resume(tmp_path):
+    schema = get_schema("adult", rows=600)
+    shards = split_table(make_table(schema, seed=5), 2)
+    cfg = CTGANConfig(batch_size=100, gen_dim=(16, 16), dis_dim=(16, 16), embedding_dim=8, sample_rows=50)
+
+    def build(resume, epochs):
+        clients = [MDGANClient(datapath="Adult_train.csv", selected_variables=schema.columns,
+                               categorical_list=schema.categorical, nonnegative_list=[], date_dic={},
+                               target_column=schema.target, problem_type="", epochs=epochs, device="cpu", config=cfg,
+                               dataframe=sh, write_side_files=False, client_id=i, vgm_backend="vb")
+                   for i, sh in enumerate(shards)]
+        return clients, MDGANServer(clients, epochs=epochs, config=cfg, name="Adult", out_dir=str(tmp_path),
+                                    async_csv=False, checkpoint_every=1, resume=resume, vgm_backend="vb")
+
+    c1, s1 = build(False, 1)
+    federate(s1, verbose=False)
+    sd = c1[0].engine.G.state_dict()
+    c2, s2 = build(True, 2)
+    federate(s2, verbose=False)
+    assert s2.start_epoch == 1 and len(s2.round_times) == 2
+    ck = torch.load(s2.checkpoint_path(), weights_only=False)
+    assert ck["epoch"] == 2 and set(ck["clients"][0]) >= {"G", "D", "optG", "optD", "rng"}
+    assert set(sd.keys()) == set(ck["clients"][0]["G"].keys())
+    path = s2.save_model("unit")
+    obj = torch.load(path, weights_only=False)
+    assert len(obj) == 5 and obj[3] == 100
