@@ -1,0 +1,331 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a -- kind::tf32, fp32 accumulation in tensor memory.
+//
+//   D[M,N] (+)= epilogue( A[M,K] . B[N,K]^T )      (epilogue: common.cuh::ftg_epilogue_store)
+//
+// * operands are fp32 in global memory; TMA (cp.async.bulk.tensor.2d, SWIZZLE_128B) stages
+//   them into shared memory, the tensor core reads them as tf32, the accumulator tile
+//   (128 lanes x 64 columns fp32) lives in TMEM and is read back with tcgen05.ld;
+// * both operand majors are supported natively (K-major: [rows, K]; MN-major: [K, rows]),
+//   so forward (X.W^T), dgrad (dY.W) and wgrad (dY^T.X) need no transposed copies;
+// * warp roles: warp 0 lane 0 = TMA producer, warp 1 = TMEM allocator + lane 0 MMA issuer,
+//   warps 2..5 = epilogue (each owns one 32-lane TMEM quadrant); 4-stage mbarrier ring;
+// * split-K: grid.z CTAs write partial tiles to a caller-provided workspace; the CTA that
+//   arrives last at the tile's counter reduces them in fixed z order (deterministic) and
+//   applies the fused epilogue.  The CTGAN shapes are skinny (M = 50..500, K up to ~8000),
+//   so split-K is what fills the 148 SMs.
+#include "common.cuh"
+#include <cuda.h>
+#include <mutex>
+
+namespace {
+
+constexpr int BM = 128, BN = 64, BK = 32;       // BK floats = 128 B = one swizzle row
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = BM * BK * 4;      // 16 KB
+constexpr int B_STAGE_BYTES = BN * BK * 4;      //  8 KB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int TMEM_COLS = 64;
+constexpr int NUM_THREADS = 192;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr uint32_t SPIN_LIMIT = 1u << 24;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0, spins = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (!done && ++spins > SPIN_LIMIT) __trap();   // never hang the GPU on a protocol bug
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+// Shared-memory matrix descriptor (SWIZZLE_128B, sm_100 descriptor version 1).
+//   bits [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout=2
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+          const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;            // SWIZZLE_128B tiles need 1024 B alignment
+  unsigned char* gen_base = smem_raw + (base - raw);
+  const uint32_t bars = base + STAGES * STAGE_BYTES;      // full[S], empty[S], tmem_full, tmem_slot, flag
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + STAGES * STAGE_BYTES + 8 * (2 * STAGES + 1));
+  volatile int* last_flag = reinterpret_cast<volatile int*>(gen_base + STAGES * STAGE_BYTES + 8 * (2 * STAGES + 1) + 8);
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+  const uint32_t tmem_full_bar = bars + 8u * (2 * STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM, z = blockIdx.z;
+  const int nkb = (p.K + BK - 1) / BK;
+  const int kb0 = (int)((long long)z * nkb / split_k), kb1 = (int)((long long)(z + 1) * nkb / split_k);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    int s = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(empty_bar(s), phase ^ 1u);
+      const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
+      mbar_expect_tx(full_bar(s), STAGE_BYTES);
+      const int k = kb * BK;
+      if (A_MN) {
+#pragma unroll
+        for (int c = 0; c < BM / 32; ++c) tma_load_2d(sa + c * (BK * 128), &map_a, full_bar(s), m0 + c * 32, k);
+      } else {
+        tma_load_2d(sa, &map_a, full_bar(s), k, m0);
+      }
+      if (B_MN) {
+#pragma unroll
+        for (int c = 0; c < BN / 32; ++c) tma_load_2d(sb + c * (BK * 128), &map_b, full_bar(s), n0 + c * 32, k);
+      } else {
+        tma_load_2d(sb, &map_b, full_bar(s), k, n0);
+      }
+      if (++s == STAGES) { s = 0; phase ^= 1u; }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // -------------------------------------------------------------- MMA issuer
+    // instruction descriptor: D=f32, A=B=tf32, majors, N=64, M=128
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    int s = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(full_bar(s), phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
+#pragma unroll
+      for (int ks = 0; ks < BK / 8; ++ks) {
+        // K-major: 8 tf32 = 32 B step inside the 128 B swizzle row; SBO = 8 rows * 128 B
+        // MN-major: 8 k-rows = 1024 B step; LBO = next 32-element MN chunk, SBO = next 8-k group
+        uint64_t ad = A_MN ? make_desc(sa + ks * 1024, BK * 128, 1024) : make_desc(sa + ks * 32, 16, 1024);
+        uint64_t bd = B_MN ? make_desc(sb + ks * 1024, BK * 128, 1024) : make_desc(sb + ks * 32, 16, 1024);
+        umma_tf32(tmem_base, ad, bd, idesc, (kb > kb0 || ks > 0) ? 1u : 0u);
+      }
+      umma_commit(empty_bar(s));                // frees the smem slot when these MMAs retire
+      if (++s == STAGES) { s = 0; phase ^= 1u; }
+    }
+    umma_commit(tmem_full_bar);                 // accumulator complete
+  } else if (warp >= 2) {
+    // ---------------------------------------------------------------- epilogue
+    const int q = warp & 3;                      // TMEM lane quadrant owned by this warp
+    const int row_in_tile = q * 32 + lane;
+    const int m = m0 + row_in_tile;
+    mbar_wait(tmem_full_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    uint32_t r[64];
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    tmem_ld32(taddr, r);
+    tmem_ld32(taddr + 32, r + 32);
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    if (split_k == 1) {
+      if (m < p.M) {
+#pragma unroll
+        for (int j = 0; j < BN; ++j) {
+          int n = n0 + j;
+          if (n < p.N) ftg_epilogue_store(p, m, n, __uint_as_float(r[j]));
+        }
+      }
+    } else {
+      const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+      const int n_tiles = gridDim.x * gridDim.y;
+      float* ws = workspace + ((size_t)z * n_tiles + tile) * (BM * BN) + (size_t)row_in_tile * BN;
+#pragma unroll
+      for (int j = 0; j < BN; j += 4)
+        *reinterpret_cast<float4*>(ws + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                                          __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 64) {
+        int old = atomicAdd(&tile_counters[tile], 1);
+        *last_flag = (old == split_k - 1) ? 1 : 0;
+        if (old == split_k - 1) tile_counters[tile] = 0;   // re-arm for the next launch
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*last_flag) {
+        __threadfence();
+        if (m < p.M) {
+          const float* wsr = workspace + (size_t)tile * (BM * BN) + (size_t)row_in_tile * BN;
+          const size_t zstride = (size_t)n_tiles * (BM * BN);
+#pragma unroll 4
+          for (int j = 0; j < BN; j += 4) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int zz = 0; zz < split_k; ++zz) {
+              float4 v = __ldcg(reinterpret_cast<const float4*>(wsr + zz * zstride + j));
+              acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            int n = n0 + j;
+            if (n < p.N) ftg_epilogue_store(p, m, n, acc.x);
+            if (n + 1 < p.N) ftg_epilogue_store(p, m, n + 1, acc.y);
+            if (n + 2 < p.N) ftg_epilogue_store(p, m, n + 2, acc.z);
+            if (n + 3 < p.N) ftg_epilogue_store(p, m, n + 3, acc.w);
+          }
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// 2-D fp32 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld floats.
+bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, int box_inner, int box_outer) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+template <bool A_MN, bool B_MN>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
+           cudaStream_t stream) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
+  k_gemm_tc<A_MN, B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr);
+  ++g_ftg_launch_count;
+  return (int)cudaPeekAtLastError();
+}
+
+}  // namespace
+
+extern "C" int ftg_gemm_tc_num_tiles(int M, int N) { return ftg_cdiv(M, BM) * ftg_cdiv(N, BN); }
+
+extern "C" long long ftg_gemm_tc_workspace_bytes(int M, int N, int split_k) {
+  if (split_k <= 1) return 0;
+  return (long long)split_k * ftg_gemm_tc_num_tiles(M, N) * BM * BN * 4;
+}
+
+// Heuristic: split K until the grid covers ~1 wave of 148 SMs, keeping >= 4 k-blocks per CTA.
+extern "C" int ftg_gemm_tc_choose_split(int M, int N, int K) {
+  int tiles = ftg_gemm_tc_num_tiles(M, N);
+  int nkb = ftg_cdiv(K, BK);
+  int s = 148 / (tiles > 0 ? tiles : 1);
+  int cap = nkb / 4;
+  if (s > cap) s = cap;
+  if (s > 32) s = 32;
+  if (s < 1) s = 1;
+  return s;
+}
+
+extern "C" int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* workspace, int* tile_counters,
+                           ftg_stream_t stream) {
+  const ftg_gemm_args& p = *args;
+  if (p.M <= 0 || p.N <= 0) return 0;
+  if (p.K <= 0) return FTG_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(p.a) & 15) || (reinterpret_cast<uintptr_t>(p.b) & 15) || (p.lda & 3) || (p.ldb & 3))
+    return FTG_ERR_UNSUPPORTED;
+  const int nkb = ftg_cdiv(p.K, BK);
+  if (split_k < 1) split_k = 1;
+  if (split_k > nkb) split_k = nkb;
+  if (split_k > 1 && (!workspace || !tile_counters)) return FTG_ERR_UNSUPPORTED;
+  CUtensorMap ma, mb;
+  bool ok = p.a_t ? make_map(&ma, p.a, p.M, p.K, p.lda, 32, BK) : make_map(&ma, p.a, p.K, p.M, p.lda, BK, BM);
+  ok = ok && (p.b_t ? make_map(&mb, p.b, p.N, p.K, p.ldb, 32, BK) : make_map(&mb, p.b, p.K, p.N, p.ldb, BK, BN));
+  if (!ok) return FTG_ERR_UNSUPPORTED;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (p.a_t) return p.b_t ? launch<true, true>(ma, mb, p, split_k, workspace, tile_counters, s)
+                          : launch<true, false>(ma, mb, p, split_k, workspace, tile_counters, s);
+  return p.b_t ? launch<false, true>(ma, mb, p, split_k, workspace, tile_counters, s)
+               : launch<false, false>(ma, mb, p, split_k, workspace, tile_counters, s);
+}

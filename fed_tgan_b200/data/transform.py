@@ -38,8 +38,10 @@ def _expm1_column(x: np.ndarray):
 
 class Transform:
     @staticmethod
-    def decode_arrays(data, meta_json, LEs):
-        """Return ``(column_names, list_of_column_arrays)`` with decoded values."""
+    def decode_arrays(data, meta_json, LEs, as_codes=False):
+        """Return ``(column_names, list_of_column_arrays)`` with decoded values.  With
+        ``as_codes`` categorical columns come back as ``(int32 codes, class strings)`` pairs
+        (what the native CSV writer consumes) instead of object arrays."""
         meta = _load_meta(meta_json)
         names = [c["column_name"] for c in meta["columns"]]
         data = np.asarray(data)
@@ -48,7 +50,11 @@ class Transform:
         cols = []
         for j, name in enumerate(names):
             raw = data[:, j]
-            if name in le_by_col:
+            if name in le_by_col and as_codes:
+                classes = [" " if str(c) == EMPTY_TOKEN else str(c) for c in le_by_col[name].classes_]
+                codes = np.clip(raw.astype(np.int64), 0, len(classes) - 1).astype(np.int32)
+                cols.append((codes, classes))
+            elif name in le_by_col:
                 vals = le_by_col[name].inverse_transform(raw.astype(np.int64))
                 if vals.dtype.kind in "OUS":
                     vals = np.where(vals == EMPTY_TOKEN, " ", vals)

@@ -1,0 +1,479 @@
+"""ctypes bindings of ``libfedtgan_b200.so`` with the same signatures as ``ops.reference``.
+
+Importing this module loads the in-tree shared object (building it first if the sources
+are newer) and raises if that is impossible -- on a GPU box there is no silent PyTorch
+fallback.  All launches go to ``torch.cuda.current_stream()``, so they order with the
+caller's PyTorch work and are CUDA-graph capturable.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+from . import build as _build
+
+_LIB_PATH = _build.LIB
+if os.environ.get("FEDTGAN_NO_BUILD", "0") != "1":
+    try:
+        _LIB_PATH = _build.build()
+    except Exception:  # no nvcc on this box: use the shipped .so
+        if not os.path.exists(_LIB_PATH):
+            raise
+lib = C.CDLL(_LIB_PATH)
+
+UNSUPPORTED = 1000
+_vp, _i, _f, _ll = C.c_void_p, C.c_int, C.c_float, C.c_longlong
+
+
+class GemmArgs(C.Structure):
+    _fields_ = [
+        ("a", _vp), ("b", _vp), ("d", _vp),
+        ("M", _i), ("N", _i), ("K", _i),
+        ("lda", _i), ("ldb", _i), ("ldd", _i),
+        ("a_t", _i), ("b_t", _i),
+        ("bias", _vp),
+        ("act", _i),
+        ("mask_in", _vp), ("ld_mask_in", _i),
+        ("mask_out", _vp), ("ld_mask_out", _i),
+        ("drop_u", _vp), ("ld_drop_u", _i),
+        ("rng_state", _vp), ("rng_stream", _i),
+        ("alpha", _f), ("slope", _f), ("drop_p", _f),
+        ("accumulate", _i),
+    ]
+
+
+def _sig(name, argtypes, restype=_i):
+    fn = getattr(lib, name)
+    fn.argtypes = argtypes
+    fn.restype = restype
+    return fn
+
+
+_gemm_simt = _sig("ftg_gemm_simt", [C.POINTER(GemmArgs), _vp])
+_gemm_tc = _sig("ftg_gemm_tc", [C.POINTER(GemmArgs), _i, _vp, _vp, _vp])
+_choose_split = _sig("ftg_gemm_tc_choose_split", [_i, _i, _i])
+_ws_bytes = _sig("ftg_gemm_tc_workspace_bytes", [_i, _i, _i], _ll)
+_num_tiles = _sig("ftg_gemm_tc_num_tiles", [_i, _i])
+_rowdot = _sig("ftg_rowdot", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp])
+_colsum = _sig("ftg_colsum", [_vp, _i, _i, _i, _vp, _vp, _i, _vp])
+_som = _sig("ftg_scale_outer_mask", [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp])
+_bn_fwd = _sig("ftg_bn_relu_fwd", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp])
+_bn_bwd = _sig("ftg_bn_relu_bwd", [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp])
+_act_fwd = _sig("ftg_activate_fwd", [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _f, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp])
+_act_bwd = _sig("ftg_activate_bwd", [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _f, _i, _vp])
+_cond_loss = _sig("ftg_cond_loss", [_vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp])
+_slerp = _sig("ftg_slerp", [_vp, _i, _vp, _i, _vp, _i, _i, _i, _vp, _vp, _i, _vp])
+_gp = _sig("ftg_gp_penalty", [_vp, _i, _i, _i, _vp, _f, _vp])
+_adam = _sig("ftg_adam", [_vp, _vp, _vp, _vp, _ll, _vp, _f, _f, _f, _f, _f, _vp])
+_tick = _sig("ftg_tick", [_vp, _vp])
+_fill_normal = _sig("ftg_fill_normal", [_vp, _i, _i, _i, _vp, _i, _vp])
+_sample_condvec = _sig("ftg_sample_condvec", [_vp, _i, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp])
+_write_condvec = _sig("ftg_write_condvec", [_vp, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _vp])
+_argsort = _sig("ftg_argsort_perm", [_vp, _i, _vp, _vp, _i, _vp])
+_sample_rows = _sig("ftg_sample_rows", [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp])
+_expand_rows = _sig("ftg_expand_rows", [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp])
+_vgm_decode = _sig("ftg_vgm_decode", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp])
+_vgm_encode = _sig("ftg_vgm_encode", [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _vp, _i, _vp])
+_fedavg_local = _sig("ftg_fedavg_local", [_vp, _i, _vp, _ll, _vp, _i, _vp])
+_fedavg_twoshot = _sig("ftg_fedavg_twoshot", [_vp, _vp, _i, _i, _vp, _ll, _vp, _i, _i, _vp, _i, _vp])
+_fedavg_oneshot = _sig("ftg_fedavg_oneshot", [_vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _i, _i, _vp, _i, _vp])
+_symm_alloc = _sig("ftg_symm_alloc", [_ll, C.POINTER(_vp)])
+_symm_free = _sig("ftg_symm_free", [_vp])
+_symm_export = _sig("ftg_symm_export", [_vp, C.c_char_p])
+_symm_open = _sig("ftg_symm_open", [C.c_char_p, C.POINTER(_vp)])
+_symm_close = _sig("ftg_symm_close", [_vp])
+_stats = _sig("ftg_stats_to_weights", [_vp, _i, _i, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp])
+_launch_count = _sig("ftg_last_launch_count", [])
+lib.ftg_version.restype = C.c_char_p
+
+
+def version() -> str:
+    return lib.ftg_version().decode()
+
+
+def launch_count() -> int:
+    return int(_launch_count())
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _ck(rc, what):
+    if rc != 0:
+        raise NativeError(f"{what} failed with code {rc}")
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def _m(t):
+    """(ptr, ld) of a 2-D fp32 view with unit column stride."""
+    if t is None:
+        return None, 0
+    assert t.dtype == torch.float32 and t.dim() == 2 and (t.shape[1] == 1 or t.stride(1) == 1), (t.dtype, t.shape, t.stride())
+    return t.data_ptr(), (t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1))
+
+
+def _ld(t):
+    return t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1)
+
+
+# ----------------------------------------------------------------- precision
+_precision = os.environ.get("FEDTGAN_PRECISION", "tf32")
+_scratch = {}
+MAX_WS_BYTES = 64 << 20
+
+
+def set_precision(p: str):
+    global _precision
+    assert p in ("tf32", "fp32")
+    _precision = p
+
+
+def get_precision() -> str:
+    return _precision
+
+
+def _scratch_for(device, stream):
+    key = (device.index, stream)
+    if key not in _scratch:
+        _scratch[key] = (torch.empty(MAX_WS_BYTES // 4, dtype=torch.float32, device=device),
+                         torch.zeros(8192, dtype=torch.int32, device=device))
+    return _scratch[key]
+
+
+def preallocate_scratch(device):
+    """Allocate the split-K scratch for the current stream (call before graph capture)."""
+    return _scratch_for(torch.device(device), _stream())
+
+
+# ---------------------------------------------------------------------- GEMM
+def _gemm_args(a, b, out, a_t, b_t, bias, act, mask_in, mask_out, u, rng, stream, accumulate, alpha, slope, p):
+    M, N = out.shape
+    K = a.shape[0] if a_t else a.shape[1]
+    assert (a.shape[1] if a_t else a.shape[0]) == M, (a.shape, out.shape, a_t)
+    assert (b.shape[1] if b_t else b.shape[0]) == N and (b.shape[0] if b_t else b.shape[1]) == K, (b.shape, N, K, b_t)
+    g = GemmArgs()
+    g.a, g.lda = _m(a)
+    g.b, g.ldb = _m(b)
+    g.d, g.ldd = _m(out)
+    g.M, g.N, g.K = M, N, K
+    g.a_t, g.b_t = int(a_t), int(b_t)
+    g.bias = _p(bias)
+    g.act = {None: 0, "leaky": 1, "leaky_dropout": 2}[act]
+    g.mask_in, g.ld_mask_in = _m(mask_in)
+    g.mask_out, g.ld_mask_out = _m(mask_out)
+    g.drop_u, g.ld_drop_u = _m(u)
+    g.rng_state = _p(rng.state) if rng is not None else None
+    g.rng_stream = int(stream)
+    g.alpha, g.slope, g.drop_p = float(alpha), float(slope), float(p)
+    g.accumulate = int(accumulate)
+    if g.act == 2 and u is None and rng is None:
+        raise ValueError("dropout needs uniforms or an rng")
+    return g
+
+
+def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None, mask_out=None, u=None, rng=None,
+           stream=0, accumulate=False, alpha=1.0, slope=0.2, p=0.5, precision=None, split_k=None):
+    g = _gemm_args(a, b, out, a_t, b_t, bias, act, mask_in, mask_out, u, rng, stream, accumulate, alpha, slope, p)
+    prec = precision or _precision
+    st = _stream()
+    if prec == "tf32":
+        sk = split_k if split_k is not None else _choose_split(g.M, g.N, g.K)
+        ws = ctr = None
+        if sk > 1:
+            wsb, ctrb = _scratch_for(out.device, st)
+            while sk > 1 and _ws_bytes(g.M, g.N, sk) > MAX_WS_BYTES:
+                sk -= 1
+            if _num_tiles(g.M, g.N) > ctrb.numel():
+                sk = 1
+            ws, ctr = wsb.data_ptr(), ctrb.data_ptr()
+        rc = _gemm_tc(C.byref(g), sk, ws, ctr, st)
+        if rc == 0:
+            return out
+        if rc != UNSUPPORTED:
+            raise NativeError(f"ftg_gemm_tc failed with code {rc}")
+    _ck(_gemm_simt(C.byref(g), st), "ftg_gemm_simt")
+    return out
+
+
+def rowdot(a, w, bias, out):
+    pa, lda = _m(a)
+    _ck(_rowdot(pa, lda, a.shape[0], a.shape[1], _p(w), _p(bias), _p(out), _stream()), "rowdot")
+    return out
+
+
+def colsum(a, out, rowscale=None, accumulate=False):
+    pa, lda = _m(a)
+    _ck(_colsum(pa, lda, a.shape[0], a.shape[1], _p(rowscale), _p(out), int(accumulate), _stream()), "colsum")
+    return out
+
+
+def scale_outer_mask(rowscale, v, mask, out):
+    pm, ldm = _m(mask)
+    po, ldo = _m(out)
+    _ck(_som(_p(rowscale), _p(v), pm, ldm, po, ldo, out.shape[0], out.shape[1], _stream()), "scale_outer_mask")
+    return out
+
+
+def bn_relu_fwd(a, gamma, beta, running_mean, running_var, out, save_mean, save_invstd, *, training=True, eps=1e-5,
+                momentum=0.1, num_batches_tracked=None):
+    pa, lda = _m(a)
+    po, ldo = _m(out)
+    _ck(_bn_fwd(pa, lda, a.shape[0], a.shape[1], _p(gamma), _p(beta), _p(running_mean), _p(running_var), po, ldo,
+                _p(save_mean), _p(save_invstd), int(training), float(eps), float(momentum),
+                _p(num_batches_tracked), _stream()), "bn_relu_fwd")
+    return out
+
+
+def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta):
+    pd, ldd = _m(dout)
+    pa, lda = _m(a)
+    pda, ldda = _m(da)
+    _ck(_bn_bwd(pd, ldd, pa, lda, a.shape[0], a.shape[1], _p(save_mean), _p(save_invstd), _p(gamma), _p(beta), pda,
+                ldda, _p(dgamma), _p(dbeta), _stream()), "bn_relu_bwd")
+    return da
+
+
+def activate_fwd(fake, tables, out, *, tau=0.2, u=None, rng=None, stream=0, cond=None, hard_noise=True):
+    dd = tables["col_span"].numel()
+    pf, ldf = _m(fake)
+    po, ldo = _m(out)
+    pu, ldu = _m(u)
+    pc, ldc = _m(cond)
+    n_opt = cond.shape[1] if cond is not None else 0
+    _ck(_act_fwd(pf, ldf, fake.shape[0], dd, tables["span_start"].numel(), _p(tables["span_start"]),
+                 _p(tables["span_width"]), _p(tables["span_kind"]), po, ldo, float(tau), pu, ldu,
+                 _p(rng.state) if rng is not None else None, int(stream), pc, ldc, n_opt, int(hard_noise), _stream()),
+        "activate_fwd")
+    return out
+
+
+def activate_bwd(dout, act, tables, dfake, *, tau=0.2, accumulate=False):
+    pd, ldd = _m(dout)
+    pa, lda = _m(act)
+    pf, ldf = _m(dfake)
+    _ck(_act_bwd(pd, ldd, pa, lda, dout.shape[0], tables["span_start"].numel(), _p(tables["span_start"]),
+                 _p(tables["span_width"]), _p(tables["span_kind"]), pf, ldf, float(tau), int(accumulate), _stream()),
+        "activate_bwd")
+    return dfake
+
+
+def cond_loss_fwd_bwd(fake, cond, mask, tables, dfake, loss_out, *, accumulate=True):
+    pf, ldf = _m(fake)
+    pc, ldc = _m(cond)
+    pm, ldm = _m(mask)
+    pdf, lddf = _m(dfake)
+    dd = tables["col_span"].numel()
+    _ck(_cond_loss(pf, ldf, pc, ldc, pm, ldm, fake.shape[0], dd, tables["soft_start"].numel(),
+                   _p(tables["soft_start"]), _p(tables["soft_width"]), _p(tables["soft_cstart"]), pdf, lddf,
+                   _p(loss_out), int(accumulate), _stream()), "cond_loss")
+    return loss_out
+
+
+def slerp(low, high, out, *, alpha=None, rng=None, stream=0):
+    pl, ldl = _m(low)
+    ph, ldh = _m(high)
+    po, ldo = _m(out)
+    _ck(_slerp(pl, ldl, ph, ldh, po, ldo, low.shape[0], low.shape[1], _p(alpha),
+               _p(rng.state) if rng is not None else None, int(stream), _stream()), "slerp")
+    return out
+
+
+def gp_penalty(g, pen_out, *, lambda_=10.0):
+    pg, ldg = _m(g)
+    _ck(_gp(pg, ldg, g.shape[0], g.shape[1], _p(pen_out), float(lambda_), _stream()), "gp_penalty")
+    return pen_out
+
+
+def adam_step(param, grad, exp_avg, exp_avg_sq, step, *, lr, beta1, beta2, eps, weight_decay=0.0):
+    """``step`` must be a view of the device rng/step state whose element [0] is the step
+    count; the kernel reads ``state[1]`` so we pass ``step`` minus one int64."""
+    assert torch.is_tensor(step) and step.dtype == torch.int64
+    state_ptr = step.data_ptr() - 8
+    _ck(_adam(_p(param), _p(grad), _p(exp_avg), _p(exp_avg_sq), param.numel(), state_ptr, float(lr), float(beta1),
+              float(beta2), float(eps), float(weight_decay), _stream()), "adam")
+    return param
+
+
+def tick(state):
+    _ck(_tick(_p(state), _stream()), "tick")
+
+
+def fill_normal(out, *, z=None, rng=None, stream=0):
+    if z is not None:
+        out.copy_(z)
+        return out
+    po, ldo = _m(out)
+    _ck(_fill_normal(po, out.shape[0], out.shape[1], ldo, _p(rng.state), int(stream), _stream()), "fill_normal")
+    return out
+
+
+def sample_condvec(cum_p, soft_width, col_out, opt_out, *, u_col=None, u_opt=None, rng=None, stream=0):
+    _ck(_sample_condvec(_p(cum_p), cum_p.shape[0], cum_p.shape[1], _p(soft_width), _p(col_out), _p(opt_out),
+                        col_out.shape[0], _p(u_col), _p(u_opt), _p(rng.state) if rng is not None else None,
+                        int(stream), _stream()), "sample_condvec")
+    return col_out, opt_out
+
+
+def write_condvec(col, opt, soft_cstart, c_out, m_out=None, perm=None):
+    pc, ldc = _m(c_out)
+    pm, ldm = _m(m_out)
+    n_col = m_out.shape[1] if m_out is not None else 0
+    _ck(_write_condvec(_p(col), _p(opt), _p(soft_cstart), pc, ldc, c_out.shape[1], pm, ldm, n_col, _p(perm),
+                       c_out.shape[0], _stream()), "write_condvec")
+    return c_out
+
+
+def argsort_perm(perm_out, *, u=None, rng=None, stream=0):
+    _ck(_argsort(_p(perm_out), perm_out.shape[0], _p(u), _p(rng.state) if rng is not None else None, int(stream),
+                 _stream()), "argsort_perm")
+    return perm_out
+
+
+def sample_rows(row_ptr, row_ids, soft_cstart, col, opt, rid_out, *, perm=None, u=None, rng=None, stream=0):
+    _ck(_sample_rows(_p(row_ptr), _p(row_ids), _p(soft_cstart), _p(col), _p(opt), _p(perm), _p(rid_out),
+                     rid_out.shape[0], _p(u), _p(rng.state) if rng is not None else None, int(stream), _stream()),
+        "sample_rows")
+    return rid_out
+
+
+def expand_rows(vals, codes, rid, tables, out):
+    po, ldo = _m(out)
+    dd = tables["col_span"].numel()
+    _ck(_expand_rows(_p(vals), vals.shape[1], _p(codes), codes.shape[1], _p(rid), _p(tables["tanh_start"]),
+                     _p(tables["soft_start"]), po, ldo, dd, out.shape[0], _stream()), "expand_rows")
+    return out
+
+
+_decode_cache = {}
+
+
+def _decode_tables(tables, col_is_cont, cat_off, device):
+    key = (id(tables), col_is_cont.data_ptr())
+    if key not in _decode_cache:
+        cic = col_is_cont.cpu().tolist()
+        starts = tables["span_start"].cpu().tolist()
+        widths = tables["span_width"].cpu().tolist()
+        coff = cat_off.cpu().tolist()
+        col_start, col_width, col_aux = [], [], []
+        s = ci = ki = 0
+        for c in cic:
+            if c:
+                col_start.append(starts[s])
+                col_width.append(widths[s + 1])
+                col_aux.append(ci)
+                ci += 1
+                s += 2
+            else:
+                col_start.append(starts[s])
+                col_width.append(widths[s])
+                col_aux.append(coff[ki])
+                ki += 1
+                s += 1
+        mk = lambda v: torch.tensor(v, dtype=torch.int32, device=device)  # noqa: E731
+        _decode_cache[key] = (mk(cic), mk(col_start), mk(col_width), mk(col_aux))
+    return _decode_cache[key]
+
+
+def vgm_decode(act, tables, mu, sd, cat_ids, cat_off, col_is_cont, out):
+    cic, cs, cw, ca = _decode_tables(tables, col_is_cont, cat_off, act.device)
+    pa, lda = _m(act)
+    po, ldo = _m(out)
+    k = mu.shape[1] if mu.dim() == 2 and mu.numel() else 1
+    _ck(_vgm_decode(pa, lda, act.shape[0], cic.numel(), _p(cic), _p(cs), _p(cw), _p(ca), _p(mu), _p(sd), k,
+                    _p(cat_ids), po, ldo, _stream()), "vgm_decode")
+    return out
+
+
+def vgm_encode(x, logit_const, mu, var, active, u, val_out, code_out, rng=None, stream=0):
+    lc, m, v = (t[active].contiguous().float() for t in (logit_const, mu, var))
+    _ck(_vgm_encode(_p(x), x.shape[0], _p(lc), _p(m), _p(v), lc.numel(), _p(u),
+                    _p(rng.state) if rng is not None else None, int(stream), _p(val_out), val_out.stride(0),
+                    _p(code_out), code_out.stride(0), _stream()), "vgm_encode")
+    return val_out, code_out
+
+
+# ------------------------------------------------------------ federated average
+def _ptr_array(ptrs):
+    arr = (C.c_void_p * len(ptrs))(*ptrs)
+    return arr
+
+
+def fedavg_local(arenas, weights, int_offsets=()):
+    """All replicas on this GPU: one launch over all ranks' data."""
+    n = arenas[0].numel()
+    pa = _ptr_array([a.data_ptr() for a in arenas])
+    w = (C.c_float * len(arenas))(*[float(x) for x in weights])
+    io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
+    _ck(_fedavg_local(pa, len(arenas), w, n, io, len(int_offsets), _stream()), "fedavg_local")
+    return arenas
+
+
+def fedavg_twoshot(peer_ptrs, flag_ptrs, rank, weights, n, int_offsets, round_id, status, timeout_ms=20000):
+    world = len(peer_ptrs)
+    pa, fa = _ptr_array(peer_ptrs), _ptr_array(flag_ptrs)
+    w = (C.c_float * world)(*[float(x) for x in weights])
+    io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
+    _ck(_fedavg_twoshot(pa, fa, rank, world, w, n, io, len(int_offsets), int(round_id), _p(status), int(timeout_ms),
+                        _stream()), "fedavg_twoshot")
+
+
+def fedavg_oneshot(peer_ptrs, flag_ptrs, staging, rank, weights, n, int_offsets, round_id, status, timeout_ms=20000):
+    world = len(peer_ptrs)
+    pa, fa = _ptr_array(peer_ptrs), _ptr_array(flag_ptrs)
+    w = (C.c_float * world)(*[float(x) for x in weights])
+    io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
+    _ck(_fedavg_oneshot(pa, fa, _p(staging), rank, world, w, n, io, len(int_offsets), int(round_id), _p(status),
+                        int(timeout_ms), _stream()), "fedavg_oneshot")
+
+
+def symm_alloc(nbytes):
+    ptr = _vp()
+    _ck(_symm_alloc(int(nbytes), C.byref(ptr)), "symm_alloc")
+    return ptr.value
+
+
+def symm_free(ptr):
+    _ck(_symm_free(ptr), "symm_free")
+
+
+def symm_export(ptr) -> bytes:
+    buf = C.create_string_buffer(64)
+    _ck(_symm_export(ptr, buf), "symm_export")
+    return buf.raw
+
+
+def symm_open(handle: bytes):
+    ptr = _vp()
+    _ck(_symm_open(C.c_char_p(handle), C.byref(ptr)), "symm_open")
+    return ptr.value
+
+
+def symm_close(ptr):
+    _ck(_symm_close(ptr), "symm_close")
+
+
+def stats_to_weights(hist, cat_off, pool_sorted, client_sorted, smp_off, rows):
+    """Device computation of (JSD_norm [W,n_cat], WD_norm [W,n_cont], weights [W])."""
+    world = hist.shape[0]
+    n_cat = cat_off.numel() - 1
+    n_cont = pool_sorted.shape[0] if pool_sorted is not None and pool_sorted.numel() else 0
+    n_total = pool_sorted.shape[1] if n_cont else 0
+    dev = hist.device
+    jsd = torch.zeros(world, max(n_cat, 1), dtype=torch.float32, device=dev)
+    wd = torch.zeros(world, max(n_cont, 1), dtype=torch.float32, device=dev)
+    w = torch.zeros(world, dtype=torch.float32, device=dev)
+    _ck(_stats(_p(hist), world, n_cat, _p(cat_off), _p(pool_sorted) if n_cont else None, n_total,
+               _p(client_sorted) if n_cont else None, _p(smp_off) if n_cont else None, n_cont, _p(rows), _p(jsd),
+               _p(wd), _p(w), _stream()), "stats_to_weights")
+    return jsd[:, :n_cat], wd[:, :n_cont], w

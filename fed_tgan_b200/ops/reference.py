@@ -41,6 +41,13 @@ class RngState:
         return torch.randn(*shape, generator=self.gen).to(self.device)
 
     def tick(self):
+        if self.state.is_cuda:
+            import os
+            if os.environ.get("FEDTGAN_FORCE_REFERENCE", "0") != "1":
+                from . import native
+
+                native.tick(self.state)
+                return
         self.state[1] += 1
 
 

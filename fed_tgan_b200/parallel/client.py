@@ -208,6 +208,21 @@ class MDGANClient:
     def get_losses(self):
         return self.engine.losses() if self.engine is not None else {}
 
+    def read_losses(self):
+        """Device->host read of the round's losses (16 bytes)."""
+        self.last_losses = self.get_losses()
+        return self.last_losses
+
+    def restage_shard(self):
+        """Host(pinned)->device copy of this client's compact shard (out-of-core / e2e path)."""
+        return self.table.restage()
+
+    def graph_replays(self):
+        return self._graph.replays if self._graph is not None else 0
+
+    def graph_launches(self):
+        return self._graph.launches_per_replay if self._graph is not None else 0
+
     # --------------------------------------------------------------- checkpoint
     def checkpoint_state(self):
         e = self.engine

@@ -81,6 +81,7 @@ class MDGANServer:
         self._pending = []
         self.start_epoch = 0
         self.round_times = []
+        self._rid = 0
         if self.group.is_root:
             os.makedirs(self.models_dir, exist_ok=True)
             os.makedirs(self.result_dir, exist_ok=True)
@@ -213,12 +214,14 @@ class MDGANServer:
 
     def _decode_and_write(self, table_np, index):
         path = os.path.join(self.result_dir, f"{self.name}_synthesis_epoch_{index}.csv")
-        names, cols = Transform.decode_arrays(table_np, self.meta_base, self.label_encoder)
         if self.meta_base.get("date_info"):
             df, _, _ = Transform.inverse(table_np, self.meta_base, self.label_encoder)
             df.to_csv(path, index=False)
-        else:
-            write_table_csv(path, names, cols)
+            return path
+        names, cols = Transform.decode_arrays(table_np, self.meta_base, self.label_encoder, as_codes=True)
+        if any(isinstance(c, np.ndarray) and c.dtype == object for c in cols):
+            names, cols = Transform.decode_arrays(table_np, self.meta_base, self.label_encoder)
+        write_table_csv(path, names, cols)
         return path
 
     def sample_data(self, index, wait=True):
@@ -240,6 +243,11 @@ class MDGANServer:
             return None
         return self._decode_and_write(table_np, index)
 
+    def _round_id(self):
+        """Monotonic id of the next aggregation (the in-kernel barrier flags count rounds)."""
+        self._rid += 1
+        return self._rid
+
     def drain(self):
         for f in self._pending:
             f.result()
@@ -255,7 +263,7 @@ class MDGANServer:
             t_in = time.time()
             self.group.run("run_local_epochs", 1)
             t_train = time.time()
-            self.group.aggregate(w, i + 1)
+            self.group.aggregate(w, self._round_id())
             t_agg = time.time()
             self.sample_data(i, wait=not self.async_csv)
             t_out = time.time()

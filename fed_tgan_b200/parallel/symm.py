@@ -1,0 +1,87 @@
+"""Peer-visible ("symmetric") device memory for the fused aggregation kernel.
+
+Each rank allocates one block ``[arena floats | flag page]`` with ``cudaMalloc`` through the
+native library, exports its CUDA-IPC handle, and maps every peer's block.  The control
+plane (torch RPC or ``torch.distributed``) only ships the 64-byte handles once; after that
+the per-round model exchange is a single kernel per rank that loads/stores peer memory over
+NVLink and synchronises with flags in these same blocks.
+"""
+
+from __future__ import annotations
+
+import torch
+
+FLAG_INTS = 256
+
+
+class _CudaBlob:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can wrap a raw device pointer."""
+
+    def __init__(self, ptr, n_floats):
+        self.__cuda_array_interface__ = {
+            "shape": (n_floats,), "typestr": "<f4", "data": (int(ptr), False), "version": 3, "strides": None,
+        }
+
+
+class SymmetricBlock:
+    def __init__(self, n_floats: int, device):
+        from ..ops import native
+
+        self.native = native
+        self.device = torch.device(device)
+        self.n_floats = (int(n_floats) + 31) // 32 * 32
+        self.nbytes = self.n_floats * 4 + FLAG_INTS * 4
+        with torch.cuda.device(self.device):
+            self.ptr = native.symm_alloc(self.nbytes)
+            self._blob = _CudaBlob(self.ptr, self.n_floats)
+            self.tensor = torch.as_tensor(self._blob, device=self.device)
+        self.flag_ptr = self.ptr + self.n_floats * 4
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.staging = None
+        self.peer_ptrs = None
+        self.rank = None
+        self._opened = []
+
+    def export_handle(self) -> bytes:
+        return self.native.symm_export(self.ptr)
+
+    def connect(self, rank: int, handles):
+        self.rank = int(rank)
+        self.world = len(handles)
+        ptrs = []
+        with torch.cuda.device(self.device):
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    ptrs.append(self.ptr)
+                else:
+                    p = self.native.symm_open(h)
+                    self._opened.append(p)
+                    ptrs.append(p)
+        self.peer_ptrs = ptrs
+        self.peer_flag_ptrs = [p + self.n_floats * 4 for p in ptrs]
+
+    def fedavg(self, weights, n, int_offsets, round_id, mode="twoshot", timeout_ms=20000):
+        n = (int(n) + 3) // 4 * 4
+        assert n <= self.n_floats
+        with torch.cuda.device(self.device):
+            if mode == "twoshot":
+                self.native.fedavg_twoshot(self.peer_ptrs, self.peer_flag_ptrs, self.rank, weights, n, int_offsets,
+                                           round_id, self.status, timeout_ms)
+            else:
+                if self.staging is None:
+                    self.staging = torch.empty(self.n_floats, dtype=torch.float32, device=self.device)
+                self.native.fedavg_oneshot(self.peer_ptrs, self.peer_flag_ptrs, self.staging, self.rank, weights, n,
+                                           int_offsets, round_id, self.status, timeout_ms)
+
+    def check(self):
+        code = int(self.status.item())
+        if code:
+            raise RuntimeError(f"fedavg peer barrier timed out (phase {code})")
+
+    def close(self):
+        for p in self._opened:
+            try:
+                self.native.symm_close(p)
+            except Exception:
+                pass
+        self._opened = []

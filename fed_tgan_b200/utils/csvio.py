@@ -30,5 +30,6 @@ def write_table_csv(path, names, cols):
             return path
         except Exception:
             pass
-    pd.DataFrame({n: c for n, c in zip(names, cols)}, columns=list(names)).to_csv(path, index=False)
+    plain = [np.asarray(c[1], dtype=object)[c[0]] if isinstance(c, tuple) else c for c in cols]
+    pd.DataFrame({n: c for n, c in zip(names, plain)}, columns=list(names)).to_csv(path, index=False)
     return path

@@ -1,0 +1,180 @@
+/* fedtgan_b200 -- C ABI of the sm_100a kernel library (libfedtgan_b200.so).
+ *
+ * Every entry point launches on the caller's stream, allocates nothing unless stated,
+ * and returns a cudaError_t value as int (0 == success).  Matrices are row-major fp32
+ * with an explicit leading dimension (floats).  Where a reference op exists, the comment
+ * cites the reference file it replaces (paths relative to the Fed-TGAN tree,
+ * S/ = Server/).  The PyTorch oracle of each function is the function of the same name
+ * in fed_tgan_b200/ops/reference.py.
+ */
+#ifndef FEDTGAN_B200_H
+#define FEDTGAN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* ftg_stream_t; /* cudaStream_t */
+
+/* ---- GEMM with fused epilogue ------------------------------------------------------
+ * D[M,N] (+)= mask_in * act(alpha * A[M,K] . B[N,K]^T + bias[n])
+ *   a_t: A stored [K,M] (M contiguous)      b_t: B stored [K,N] (N contiguous)
+ *   act: 0 none | 1 leaky(slope) | 2 leaky(slope)+dropout(p); act!=0 writes the applied
+ *        multiplier to mask_out (if non-null).  Dropout keep = (u >= p) with u from
+ *        drop_u (tests) or Philox(rng_state, rng_stream, element index).
+ * Replaces: torch Linear / LeakyReLU / Dropout and their autograd backward
+ * (S/dtds/synthesizers/ctgan.py:15-64), SURVEY K2/K3/K7.                               */
+typedef struct {
+  const float* a; const float* b; float* d;
+  int M, N, K;
+  int lda, ldb, ldd;
+  int a_t, b_t;
+  const float* bias;
+  int act;
+  const float* mask_in; int ld_mask_in;
+  float* mask_out; int ld_mask_out;
+  const float* drop_u; int ld_drop_u;
+  const int64_t* rng_state; int rng_stream;
+  float alpha, slope, drop_p;
+  int accumulate;
+} ftg_gemm_args;
+
+/* fp32 CUDA-core GEMM (exact fp32; fallback + oracle for the tensor-core path) */
+int ftg_gemm_simt(const ftg_gemm_args* args, ftg_stream_t stream);
+
+/* tcgen05 / TMEM / TMA GEMM, kind::tf32 with fp32 accumulation in tensor memory.
+ * Split-K partial tiles go through `workspace` (>= ftg_gemm_tc_workspace_bytes(...)) and
+ * `tile_counters` (int32, zero-initialised once, >= ftg_gemm_tc_num_tiles(...)); both are
+ * caller-owned scratch and may be NULL when the call does not split K.
+ * Requirements: base pointers 16 B aligned, lda/ldb multiples of 4 floats.
+ * Returns 1000 (FTG_ERR_UNSUPPORTED) when the shape/alignment cannot be handled.        */
+int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* workspace, int* tile_counters,
+                ftg_stream_t stream);
+int ftg_gemm_tc_choose_split(int M, int N, int K);
+long long ftg_gemm_tc_workspace_bytes(int M, int N, int split_k);
+int ftg_gemm_tc_num_tiles(int M, int N);
+
+/* ---- small dense helpers ------------------------------------------------ */
+int ftg_rowdot(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
+               ftg_stream_t stream);
+int ftg_colsum(const float* a, int lda, int M, int N, const float* rowscale, float* out, int accumulate,
+               ftg_stream_t stream);
+int ftg_scale_outer_mask(const float* rowscale, const float* v, const float* mask, int ldm, float* out,
+                         int ldo, int M, int N, ftg_stream_t stream);
+
+/* ---- BatchNorm1d(train/eval)+ReLU with concat-store, and its backward -------------------
+ * Replaces Residual's BatchNorm1d+ReLU+cat (S/dtds/synthesizers/ctgan.py:40-44).         */
+int ftg_bn_relu_fwd(const float* a, int lda, int B, int H, const float* gamma, const float* beta,
+                    float* running_mean, float* running_var, float* out, int ldo, float* save_mean,
+                    float* save_invstd, int training, float eps, float momentum, float* num_batches_tracked,
+                    ftg_stream_t stream);
+int ftg_bn_relu_bwd(const float* dout, int lddo, const float* a, int lda, int B, int H, const float* save_mean,
+                    const float* save_invstd, const float* gamma, const float* beta, float* da, int ldda,
+                    float* dgamma, float* dbeta, ftg_stream_t stream);
+
+/* ---- apply_activate (tanh / gumbel-softmax) fwd+bwd, cond_loss fwd+bwd --------------------
+ * Replaces apply_activate (ctgan.py:67-82) and cond_loss (ctgan.py:174-194), SURVEY K4/K5. */
+int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n_spans, const int* span_start,
+                     const int* span_width, const int* span_kind, float* out, int ldo, float tau,
+                     const float* u, int ldu, const int64_t* rng_state, int rng_stream, const float* cond,
+                     int ldc, int n_opt, int use_noise, ftg_stream_t stream);
+int ftg_activate_bwd(const float* dout, int lddo, const float* act, int lda, int B, int n_spans,
+                     const int* span_start, const int* span_width, const int* span_kind, float* dfake, int ldf,
+                     float tau, int accumulate, ftg_stream_t stream);
+int ftg_cond_loss(const float* fake, int ldf, const float* cond, int ldc, const float* mask, int ldm, int B,
+                  int dd, int n_col, const int* soft_start, const int* soft_width, const int* soft_cstart,
+                  float* dfake, int lddf, float* loss_out, int accumulate, ftg_stream_t stream);
+
+/* ---- slerp interpolation + per-pack gradient-penalty norm (ctgan.py:231-258), K6 --------- */
+int ftg_slerp(const float* low, int ldl, const float* high, int ldh, float* out, int ldo, int B, int din,
+              const float* alpha, const int64_t* rng_state, int rng_stream, ftg_stream_t stream);
+int ftg_gp_penalty(float* g, int ldg, int Bp, int Din, float* pen_out, float lambda_, ftg_stream_t stream);
+
+/* ---- fused Adam over a flat arena (torch.optim.Adam semantics, L2-in-gradient), K8 ------- */
+int ftg_adam(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n,
+             const int64_t* rng_state /* step = state[1] */, float lr, float beta1, float beta2, float eps,
+             float weight_decay, ftg_stream_t stream);
+
+/* ---- device-side sampling (Cond.sample / Sampler.sample, ctgan.py:147-228), K9-K11 ------- */
+int ftg_tick(int64_t* rng_state, ftg_stream_t stream);
+int ftg_fill_normal(float* out, int rows, int cols, int ld, const int64_t* rng_state, int rng_stream,
+                    ftg_stream_t stream);
+int ftg_sample_condvec(const float* cum_p, int n_col, int max_w, const int* soft_width, int* col_out,
+                       int* opt_out, int B, const float* u_col, const float* u_opt, const int64_t* rng_state,
+                       int rng_stream, ftg_stream_t stream);
+int ftg_write_condvec(const int* col, const int* opt, const int* soft_cstart, float* c_out, int ldc, int n_opt,
+                      float* m_out, int ldm, int n_col, const int* perm, int B, ftg_stream_t stream);
+int ftg_argsort_perm(int* perm, int B, const float* u, const int64_t* rng_state, int rng_stream,
+                     ftg_stream_t stream);
+int ftg_sample_rows(const int* row_ptr, const int* row_ids, const int* soft_cstart, const int* col,
+                    const int* opt, const int* perm, int* rid_out, int B, const float* u,
+                    const int64_t* rng_state, int rng_stream, ftg_stream_t stream);
+int ftg_expand_rows(const float* vals, int n_tanh, const int* codes, int n_col, const int* rid,
+                    const int* tanh_start, const int* soft_start, float* out, int ld, int dd, int B,
+                    ftg_stream_t stream);
+
+/* ---- VGM codec (BGM_CTGAN_Transformer.transform / inverse_transform,
+ *      S/dtds/features/transformers.py:385-464), K12/K13 ---------------------------------- */
+int ftg_vgm_decode(const float* act, int lda, int rows, int n_columns, const int* col_is_cont,
+                   const int* col_start, const int* col_width, const int* col_aux, const float* mu,
+                   const float* sd, int n_clusters, const float* cat_ids, float* out, int ldo,
+                   ftg_stream_t stream);
+int ftg_vgm_encode(const float* x, int rows, const float* logit_const, const float* mu, const float* var,
+                   int k_active, const float* u, const int64_t* rng_state, int rng_stream, float* val_out,
+                   int val_stride, int* code_out, int code_stride, ftg_stream_t stream);
+
+/* ---- federated weighted average (average_model, S/dtds/distributed.py:86-106 + the RPC
+ *      gather/broadcast R9/R10), SURVEY K1 ------------------------------------------------
+ * theta <- sum_i w_i theta_i written into every replica; `int_offsets` slots are truncated
+ * (num_batches_tracked).
+ *  ftg_fedavg_local : all replicas on this GPU, one launch over all ranks' data
+ *                     (single-GPU emulation / LocalGroup).
+ *  ftg_fedavg_twoshot / _oneshot : one launch per rank on its own GPU; `peers[r]` are
+ *     peer-mapped device pointers to every rank's arena, `flags[r]` to every rank's flag
+ *     page (>= 4*world ints, zero-initialised).  Ranks synchronise inside the kernel with
+ *     system-scope flags; `round_id` must increase by one per call.  `status` (device
+ *     int) is set non-zero if a peer did not arrive within `timeout_ms`.                   */
+/* `arenas`/`peers`/`flags`/`weights`/`int_offsets` are small HOST arrays (passed to the kernel
+ * by value); the pointers stored in them are device / peer-mapped pointers. */
+int ftg_fedavg_local(float* const* arenas, int world, const float* weights, long long n,
+                     const int* int_offsets, int n_int, ftg_stream_t stream);
+int ftg_fedavg_twoshot(float* const* peers, int* const* flags, int rank, int world, const float* weights,
+                       long long n, const int* int_offsets, int n_int, int round_id, int* status,
+                       int timeout_ms, ftg_stream_t stream);
+int ftg_fedavg_oneshot(float* const* peers, int* const* flags, float* staging, int rank, int world,
+                       const float* weights, long long n, const int* int_offsets, int n_int, int round_id,
+                       int* status, int timeout_ms, ftg_stream_t stream);
+
+/* peer-memory plumbing (cudaMalloc + CUDA IPC); the only allocating entry points */
+int ftg_symm_alloc(long long bytes, void** ptr);
+int ftg_symm_free(void* ptr);
+int ftg_symm_export(void* ptr, unsigned char handle_out[64]);
+int ftg_symm_open(const unsigned char handle[64], void** ptr);
+int ftg_symm_close(void* ptr);
+int ftg_enable_peer_access(int device, int peer);
+
+/* ---- similarity weights (uniform_meta_category / uniform_continuous_gmm /
+ *      calculate_final_weights_for_aggregation, S/dtds/distributed.py:592-783), K15 --------
+ * hist: [world][hist_len] category counts (columns concatenated, `cat_off` [n_cat+1]);
+ * pool_sorted: [n_cont][n_total] pooled GMM sample of every continuous column, sorted;
+ * client_sorted + smp_off [n_cont*world+1]: each client's sorted sample per column;
+ * rows [world].  Writes normalised JSD [world][n_cat], WD [world][n_cont] and the final
+ * soft-maxed weights [world] (device memory, read directly by the fedavg kernels).       */
+int ftg_stats_to_weights(const float* hist, int world, int n_cat, const int* cat_off, const float* pool_sorted,
+                         int n_total, const float* client_sorted, const int* smp_off, int n_cont,
+                         const float* rows, float* jsd_out, float* wd_out, float* weights_out,
+                         ftg_stream_t stream);
+
+/* ---- host-side CSV writer (S/dtds/distributed.py:586-590 DataFrame.to_csv) --------------- */
+int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
+                  const void* const* columns, const char* const* const* str_tables, int n_threads);
+
+const char* ftg_version(void);
+int ftg_last_launch_count(void);   /* kernels launched by this library since load */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,353 @@
+"""sm_100a kernels vs the fp32 PyTorch oracle of the same op (``ops.reference``)."""
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from fed_tgan_b200.ops import reference as R  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def N():
+    from fed_tgan_b200.ops import native
+
+    return native
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def rnd(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(dev())
+
+
+def uni(*shape, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return torch.rand(*shape, generator=g).to(dev())
+
+
+def padded(rows, cols, ld, seed=0):
+    """[rows, cols] view with row stride ld (multiple of 4)."""
+    buf = rnd(rows, ld, seed=seed)
+    return buf[:, :cols]
+
+
+def close(a, b, rtol, atol):
+    err = (a.double() - b.double()).abs().max().item()
+    ref = b.double().abs().max().item()
+    assert err <= atol + rtol * ref, (err, ref)
+
+
+GEMM_SHAPES = [
+    # M, N, K, a_t, b_t
+    (500, 256, 368, False, False), (50, 256, 5020, False, False), (150, 256, 256, False, True),
+    (256, 5020, 150, True, True), (50, 5020, 256, False, True), (500, 262, 880, False, False),
+    (262, 880, 500, True, True), (500, 512, 262, False, True), (37, 19, 45, False, False),
+    (129, 65, 33, True, False), (64, 64, 32, False, False),
+]
+
+
+def _gemm_case(N, M, Nn, K, a_t, b_t, prec, **epi):
+    r4 = lambda x: (x + 3) // 4 * 4  # noqa: E731
+    a = padded(K, M, r4(M) + 4, 1) if a_t else padded(M, K, r4(K) + 4, 1)
+    b = padded(K, Nn, r4(Nn), 2) if b_t else padded(Nn, K, r4(K), 2)
+    out_n = padded(M, Nn, r4(Nn) + 8, 3).clone()
+    out_r = out_n.clone()
+    kw_n, kw_r = dict(epi), dict(epi)
+    if epi.get("mask_out") is not None:
+        kw_n["mask_out"] = torch.zeros(M, Nn, device=dev())
+        kw_r["mask_out"] = torch.zeros(M, Nn, device=dev())
+    N.linear(a, b, out_n, a_t=a_t, b_t=b_t, precision=prec, **kw_n)
+    R.linear(a, b, out_r, a_t=a_t, b_t=b_t, **kw_r)
+    torch.cuda.synchronize()
+    tol = dict(rtol=2e-5, atol=1e-4) if prec == "fp32" else dict(rtol=4e-3, atol=4e-3 * (K ** 0.5) / 8)
+    close(out_n, out_r, **tol)
+    return kw_n, kw_r, tol
+
+
+@pytest.mark.parametrize("shape", GEMM_SHAPES, ids=lambda s: "x".join(map(str, s)))
+def test_gemm_fp32(N, shape):
+    _gemm_case(N, *shape, "fp32")
+
+
+@pytest.mark.parametrize("shape", GEMM_SHAPES, ids=lambda s: "x".join(map(str, s)))
+def test_gemm_tf32_tcgen05(N, shape):
+    _gemm_case(N, *shape, "tf32")
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_gemm_epilogues(N, prec):
+    M, Nn, K = 150, 256, 640
+    bias = rnd(Nn, seed=5)
+    u = uni(M, Nn, seed=6)
+    kw_n, kw_r, tol = _gemm_case(N, M, Nn, K, False, False, prec, bias=bias, act="leaky_dropout", u=u, mask_out=True)
+    # masks may differ only where the pre-activation is within rounding of 0
+    diff = (kw_n["mask_out"] != kw_r["mask_out"]).float().mean().item()
+    assert diff < (1e-5 if prec == "fp32" else 5e-3)
+    mask = (uni(M, Nn, seed=7) > 0.3).float() * 2
+    _gemm_case(N, M, Nn, K, False, True, prec, mask_in=mask)
+    _gemm_case(N, M, Nn, K, False, False, prec, accumulate=True, alpha=0.5)
+    _gemm_case(N, 50, 256, 5020, False, False, prec, bias=bias, mask_in=mask[:50])
+
+
+def test_gemm_splitk_explicit(N):
+    M, Nn, K = 150, 256, 5020
+    a, b = padded(M, K, K + 4, 1), padded(Nn, K, K, 2)
+    ref = torch.empty(M, Nn, device=dev())
+    R.linear(a, b, ref)
+    for sk in (1, 2, 7, 16):
+        out = torch.zeros(M, Nn, device=dev())
+        N.linear(a, b, out, precision="tf32", split_k=sk)
+        close(out, ref, rtol=4e-3, atol=0.05)
+    # determinism of the fixed-order split-K reduction
+    o1, o2 = torch.zeros(M, Nn, device=dev()), torch.zeros(M, Nn, device=dev())
+    N.linear(a, b, o1, precision="tf32", split_k=16)
+    N.linear(a, b, o2, precision="tf32", split_k=16)
+    assert torch.equal(o1, o2)
+
+
+def test_gemm_dropout_philox_rate(N):
+    M, Nn, K = 150, 256, 64
+    a, b = padded(M, K, K, 1), padded(Nn, K, K, 2)
+    rng = R.RngState(3, dev())
+    rng.tick()
+    out, mask = torch.empty(M, Nn, device=dev()), torch.empty(M, Nn, device=dev())
+    N.linear(a, b, out, act="leaky_dropout", mask_out=mask, rng=rng, stream=9, precision="fp32")
+    keep = (mask != 0).float().mean().item()
+    assert abs(keep - 0.5) < 0.02
+    assert set(torch.unique(mask).tolist()) <= {0.0, 0.4, 2.0}
+
+
+def test_small_dense_ops(N):
+    a = padded(150, 256, 260, 1)
+    w, bias = rnd(256, seed=2), rnd(1, seed=3)
+    o1, o2 = torch.empty(150, device=dev()), torch.empty(150, device=dev())
+    N.rowdot(a, w, bias, o1); R.rowdot(a, w, bias, o2)
+    close(o1, o2, 1e-5, 1e-4)
+    rs = rnd(150, seed=4)
+    c1, c2 = torch.empty(256, device=dev()), torch.empty(256, device=dev())
+    N.colsum(a, c1, rowscale=rs); R.colsum(a, c2, rowscale=rs)
+    close(c1, c2, 1e-5, 1e-4)
+    N.colsum(a, c1, accumulate=True); R.colsum(a, c2, accumulate=True)
+    close(c1, c2, 1e-5, 1e-4)
+    m = uni(150, 256, seed=5)
+    s1, s2 = torch.empty(150, 256, device=dev()), torch.empty(150, 256, device=dev())
+    N.scale_outer_mask(rs, w, m, s1); R.scale_outer_mask(rs, w, m, s2)
+    close(s1, s2, 1e-6, 1e-6)
+
+
+def test_bn_relu(N):
+    B, H = 500, 256
+    a = padded(B, H, H, 1) * 2 + 0.3
+    gamma, beta = rnd(H, seed=2) * 0.5 + 1, rnd(H, seed=3) * 0.2
+    st = [dict(rm=rnd(H, seed=4), rv=uni(H, seed=5) + 0.5, nbt=torch.zeros(1, device=dev())) for _ in range(2)]
+    outs, saves = [], []
+    for fn, s in zip((N.bn_relu_fwd, R.bn_relu_fwd), st):
+        buf = torch.zeros(B, H + 64, device=dev())
+        sm, si = torch.empty(H, device=dev()), torch.empty(H, device=dev())
+        fn(a, gamma, beta, s["rm"], s["rv"], buf[:, 32:32 + H], sm, si, training=True, num_batches_tracked=s["nbt"])
+        outs.append(buf); saves.append((sm, si))
+    close(outs[0], outs[1], 1e-5, 1e-5)
+    close(saves[0][0], saves[1][0], 1e-5, 1e-6); close(saves[0][1], saves[1][1], 1e-4, 1e-5)
+    close(st[0]["rm"], st[1]["rm"], 1e-5, 1e-6); close(st[0]["rv"], st[1]["rv"], 1e-5, 1e-6)
+    assert st[0]["nbt"].item() == 1.0
+    dout = rnd(B, H, seed=7)
+    res = []
+    for fn in (N.bn_relu_bwd, R.bn_relu_bwd):
+        da, dg, db = torch.empty(B, H, device=dev()), torch.empty(H, device=dev()), torch.empty(H, device=dev())
+        fn(dout, a, saves[1][0], saves[1][1], gamma, beta, da, dg, db)
+        res.append((da, dg, db))
+    for x, y in zip(*res):
+        close(x, y, 2e-5, 2e-5)
+    # eval mode, many rows
+    a2 = rnd(3000, H, seed=9)
+    e1, e2 = torch.empty(3000, H, device=dev()), torch.empty(3000, H, device=dev())
+    N.bn_relu_fwd(a2, gamma, beta, st[1]["rm"], st[1]["rv"], e1, None, None, training=False)
+    R.bn_relu_fwd(a2, gamma, beta, st[1]["rm"], st[1]["rv"], e2, None, None, training=False)
+    close(e1, e2, 1e-5, 1e-5)
+
+
+def _layout():
+    from fed_tgan_b200.features.layout import TableLayout
+
+    info = []
+    rng = np.random.default_rng(0)
+    for i in range(30):
+        if i % 3 == 0:
+            info += [(1, "tanh"), (int(rng.integers(1, 9)), "softmax")]
+        else:
+            info += [(int(rng.integers(1, 40)), "softmax")]
+    return TableLayout(info)
+
+
+def test_activate_and_cond_loss(N):
+    lay = _layout()
+    T = lay.device_tables(dev())
+    B, dd, n_opt = 500, lay.data_dim, lay.n_opt
+    fake = padded(B, dd, (dd + 3) // 4 * 4, 1)
+    u = uni(B, dd, seed=2)
+    cond = torch.zeros(B, n_opt, device=dev())
+    col = torch.randint(0, lay.n_col, (B,), device=dev())
+    opt = (torch.rand(B, device=dev()) * T["soft_width"][col]).long()
+    cond[torch.arange(B), T["soft_cstart"][col].long() + opt] = 1
+    m = torch.zeros(B, lay.n_col, device=dev()); m[torch.arange(B), col] = 1
+    o1, o2 = torch.zeros(B, dd + n_opt + 3, device=dev()), torch.zeros(B, dd + n_opt + 3, device=dev())
+    N.activate_fwd(fake, T, o1, tau=0.2, u=u, cond=cond)
+    R.activate_fwd(fake, T, o2, tau=0.2, u=u, cond=cond)
+    close(o1, o2, 1e-4, 2e-5)
+    dout = rnd(B, dd, seed=3)
+    d1, d2 = torch.zeros(B, dd + 1, device=dev()), torch.zeros(B, dd + 1, device=dev())
+    N.activate_bwd(dout, o2, T, d1, tau=0.2); R.activate_bwd(dout, o2, T, d2, tau=0.2)
+    close(d1, d2, 1e-4, 1e-5)
+    l1, l2 = torch.zeros(1, device=dev()), torch.zeros(1, device=dev())
+    N.cond_loss_fwd_bwd(fake, cond, m, T, d1, l1, accumulate=True)
+    R.cond_loss_fwd_bwd(fake, cond, m, T, d2, l2, accumulate=True)
+    close(l1, l2, 1e-4, 1e-5); close(d1, d2, 1e-4, 1e-5)
+    # philox gumbel path: rows sum to one on softmax spans
+    rng = R.RngState(1, dev()); rng.tick()
+    N.activate_fwd(fake, T, o1, tau=0.2, rng=rng, stream=5)
+    st, w = int(lay.soft_start[3]), int(lay.soft_width[3])
+    assert torch.allclose(o1[:, st:st + w].sum(1), torch.ones(B, device=dev()), atol=1e-4)
+
+
+def test_slerp_gp_adam(N):
+    B, din = 500, 417
+    low, high = padded(B, din, 420, 1), padded(B, din, 420, 2)
+    alpha = uni(B, seed=3)
+    o1, o2 = torch.zeros(B, 420, device=dev()), torch.zeros(B, 420, device=dev())
+    N.slerp(low, high, o1[:, :din], alpha=alpha); R.slerp(low, high, o2[:, :din], alpha=alpha)
+    close(o1, o2, 1e-4, 1e-4)
+    g1 = rnd(50, 4200, seed=4) * 0.02; g2 = g1.clone()
+    p1, p2 = torch.zeros(1, device=dev()), torch.zeros(1, device=dev())
+    N.gp_penalty(g1, p1, lambda_=10.0); R.gp_penalty(g2, p2, lambda_=10.0)
+    close(p1, p2, 1e-4, 1e-5); close(g1, g2, 1e-4, 1e-7)
+    n = 10007 * 4
+    rng = R.RngState(0, dev())
+    P = [rnd(n, seed=5).clone() for _ in range(2)]
+    G = rnd(n, seed=6) * 0.1
+    Mo = [torch.zeros(n, device=dev()) for _ in range(2)]
+    V = [torch.zeros(n, device=dev()) for _ in range(2)]
+    for t in range(3):
+        rng.tick()
+        N.adam_step(P[0], G, Mo[0], V[0], rng.state[1:2], lr=2e-4, beta1=0.5, beta2=0.9, eps=1e-8, weight_decay=1e-6)
+        R.adam_step(P[1], G, Mo[1], V[1], rng.state[1:2], lr=2e-4, beta1=0.5, beta2=0.9, eps=1e-8, weight_decay=1e-6)
+    close(P[0], P[1], 1e-6, 1e-6)
+
+
+def test_sampling_ops(N):
+    from fed_tgan_b200.engine import DeviceTable
+
+    lay = _layout()
+    rng = np.random.default_rng(1)
+    rows = 4000
+    vals = rng.uniform(-1, 1, (rows, lay.n_tanh)).astype(np.float32)
+    codes = np.stack([rng.integers(0, w, rows) for w in lay.soft_width], 1).astype(np.int32)
+    t = DeviceTable(vals, codes, lay, dev())
+    T = t.tables
+    B = 500
+    ucol, uopt, uperm, urow = uni(B, seed=1), uni(B, seed=2), uni(B, seed=3), uni(B, seed=4)
+    i32 = lambda: torch.zeros(B, dtype=torch.int32, device=dev())  # noqa: E731
+    c1, o1, c2, o2 = i32(), i32(), i32(), i32()
+    N.sample_condvec(t.cum_p, T["soft_width"], c1, o1, u_col=ucol, u_opt=uopt)
+    R.sample_condvec(t.cum_p, T["soft_width"], c2, o2, u_col=ucol, u_opt=uopt)
+    assert torch.equal(c1, c2) and torch.equal(o1, o2)
+    p1, p2 = i32(), i32()
+    N.argsort_perm(p1, u=uperm); R.argsort_perm(p2, u=uperm)
+    assert torch.equal(p1, p2)
+    r1, r2 = i32(), i32()
+    N.sample_rows(t.row_ptr, t.row_ids, T["soft_cstart"], c1, o1, r1, perm=p1, u=urow)
+    R.sample_rows(t.row_ptr, t.row_ids, T["soft_cstart"], c1, o1, r2, perm=p1, u=urow)
+    assert torch.equal(r1, r2)
+    x1, x2 = torch.ones(B, lay.data_dim + lay.n_opt + 2, device=dev()), torch.ones(B, lay.data_dim + lay.n_opt + 2, device=dev())
+    N.expand_rows(t.vals, t.codes, r1, T, x1); R.expand_rows(t.vals, t.codes, r1, T, x2)
+    dd = lay.data_dim
+    N.write_condvec(c1, o1, T["soft_cstart"], x1[:, dd:dd + lay.n_opt], None, p1)
+    R.write_condvec(c1, o1, T["soft_cstart"], x2[:, dd:dd + lay.n_opt], None, p1)
+    assert torch.equal(x1, x2)
+    m1, m2 = torch.ones(B, lay.n_col, device=dev()), torch.ones(B, lay.n_col, device=dev())
+    N.write_condvec(c1, o1, T["soft_cstart"], x1[:, dd:dd + lay.n_opt], m1)
+    R.write_condvec(c1, o1, T["soft_cstart"], x2[:, dd:dd + lay.n_opt], m2)
+    assert torch.equal(m1, m2) and torch.equal(x1, x2)
+    # philox paths: distributional sanity
+    st = R.RngState(7, dev()); st.tick()
+    z = torch.zeros(500, 128, device=dev())
+    N.fill_normal(z, rng=st, stream=0)
+    assert abs(z.mean().item()) < 0.02 and abs(z.std().item() - 1) < 0.02
+    N.argsort_perm(p1, rng=st, stream=3)
+    assert sorted(p1.tolist()) == list(range(B))
+    N.sample_condvec(t.cum_p, T["soft_width"], c1, o1, rng=st, stream=1)
+    assert int(c1.max()) < lay.n_col and bool((o1 < T["soft_width"][c1.long()]).all())
+    st.tick()
+    z2 = torch.zeros(500, 128, device=dev())
+    N.fill_normal(z2, rng=st, stream=0)
+    assert not torch.equal(z, z2)
+
+
+def test_vgm_codec(N):
+    from fed_tgan_b200.features.transformers import BGM_CTGAN_Transformer
+
+    rng = np.random.default_rng(0)
+    n = 3000
+    data = np.stack([np.concatenate([rng.normal(0, 1, n // 2), rng.normal(8, 1, n // 2)]),
+                     rng.integers(0, 5, n).astype(float), rng.exponential(2, n)], 1)
+    t = BGM_CTGAN_Transformer(backend="vb", seed=0)
+    t.fit(data, (1,))
+    dense = torch.tensor(t.transform(data), dtype=torch.float32, device=dev())
+    dec = {k: torch.as_tensor(v).to(dev()) for k, v in t.decode_tables().items()}
+    T = t.layout.device_tables(dev())
+    o1 = torch.empty(n, 3, device=dev()); o2 = torch.empty(n, 3, device=dev())
+    N.vgm_decode(dense, T, dec["mu"], dec["sd"], dec["cat_ids"], dec["cat_off"], dec["col_is_cont"], o1)
+    R.vgm_decode(dense, T, dec["mu"], dec["sd"], dec["cat_ids"], dec["cat_off"], dec["col_is_cont"], o2)
+    close(o1, o2, 1e-5, 1e-5)
+    gm, mask = t.model[0], t.components[0]
+    x = torch.tensor(data[:, 0], dtype=torch.float32, device=dev())
+    lc = torch.tensor(gm.logit_const(), dtype=torch.float32, device=dev())
+    mu = torch.tensor(gm.means, dtype=torch.float32, device=dev())
+    var = torch.tensor(gm.covs, dtype=torch.float32, device=dev())
+    act = torch.tensor(mask, device=dev())
+    u = uni(n, seed=3)
+    v1, v2 = torch.empty(n, device=dev()), torch.empty(n, device=dev())
+    k1, k2 = torch.empty(n, dtype=torch.int32, device=dev()), torch.empty(n, dtype=torch.int32, device=dev())
+    N.vgm_encode(x, lc, mu, var, act, u, v1, k1); R.vgm_encode(x, lc, mu, var, act, u, v2, k2)
+    assert (k1 != k2).float().mean().item() < 2e-3
+    same = k1 == k2
+    close(v1[same], v2[same], 1e-4, 1e-4)
+
+
+def test_fedavg_local_and_stats(N):
+    world, n = 4, 4096 * 3 + 64
+    arenas = [rnd(n, seed=i) for i in range(world)]
+    for a in arenas:
+        a[100] = 7.0 + torch.rand(1).item()
+    w = [0.1, 0.2, 0.3, 0.4]
+    ref = [a.clone() for a in arenas]
+    R.fedavg(ref, w, [100])
+    N.fedavg_local(arenas, w, [100])
+    torch.cuda.synchronize()
+    for a, r in zip(arenas, ref):
+        close(a, r, 1e-6, 1e-6)
+    assert float(arenas[0][100]) == float(int(arenas[0][100]))
+    # stats -> weights vs numpy restatement
+    from fed_tgan_b200.parallel import weights as W
+
+    rng = np.random.default_rng(0)
+    sizes = [3, 7, 2]
+    hist = [np.concatenate([rng.integers(1, 50, k) for k in sizes]).astype(np.float32) for _ in range(world)]
+    cat_off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    rows = np.array([1000, 3000, 500, 1500], dtype=np.float32)
+    samples = [[np.sort(rng.normal(i * 0.5 + c, 1 + 0.1 * c, int(rows[i] / 10))).astype(np.float32) for i in range(world)]
+               for c in range(2)]
+    pool = np.stack([np.sort(np.concatenate(s)) for s in samples])
+    flat = np.concatenate([x for s in samples for x in s])
+    off = np.concatenate([[0], np.cumsum([len(x) for s in samples for x in s])]).astype(np.int32)
+    t = lambda x: torch.as_tensor(x).to(dev())  # noqa: E731
+    jsd, wd, wt = N.stats_to_weights(t(np.stack(hist)), t(cat_off), t(pool), t(flat), t(off), t(rows))
+    cv = [[h[cat_off[c]:cat_off[c + 1]] for h in hist] for c in range(3)]
+    jr, wr = W.categorical_similarity(cv), W.continuous_similarity(samples)
+    assert np.allclose(jsd.cpu().numpy(), jr, atol=2e-4)
+    assert np.allclose(wd.cpu().numpy(), wr, atol=2e-3)
+    assert np.allclose(wt.cpu().numpy(), W.final_weights(jr, wr, rows), atol=1e-4)
