@@ -179,46 +179,65 @@ extern "C" int ftg_expand_rows(const float* vals, int n_tanh, const int* codes, 
 }
 
 // -------------------------------------------------------------------- rowdot
-__global__ void k_rowdot(const float* __restrict__ a, int lda, int M, int K, const float* __restrict__ w,
-                         const float* bias, float* out) {
-  int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  int lane = threadIdx.x & 31;
-  if (row >= M) return;
-  float s = 0.f;
-  for (int k = lane; k < K; k += 32) s += a[(size_t)row * lda + k] * __ldg(w + k);
-  s = warp_sum(s);
-  if (lane == 0) out[row] = s + (bias ? bias[0] : 0.f);
+// out[m] = a[m,:].w + bias ; optionally loss_out = sum_m rowscale[m] * out[m] (fused WGAN loss value).
+// M is a few hundred at most: one CTA, one warp per row, deterministic block reduction.
+__global__ void __launch_bounds__(1024) k_rowdot(const float* __restrict__ a, int lda, int M, int K,
+                                                 const float* __restrict__ w, const float* bias, float* out,
+                                                 const float* __restrict__ rowscale, float* loss_out) {
+  __shared__ float red[32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  float contrib = 0.f;
+  for (int row = blockIdx.x * nw + wid; row < M; row += gridDim.x * nw) {
+    float s = 0.f;
+    for (int k = lane; k < K; k += 32) s += a[(size_t)row * lda + k] * __ldg(w + k);
+    s = warp_sum(s) + (bias ? bias[0] : 0.f);
+    if (lane == 0) {
+      out[row] = s;
+      if (rowscale) contrib += rowscale[row] * s;
+    }
+  }
+  if (loss_out) {
+    float tot = block_sum(contrib, red);
+    if (threadIdx.x == 0) loss_out[0] = tot;
+  }
 }
 
 extern "C" int ftg_rowdot(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
                           ftg_stream_t stream) {
-  k_rowdot<<<ftg_cdiv(M, 4), 128, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, out);
+  k_rowdot<<<ftg_cdiv(M, 32), 1024, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, out, nullptr, nullptr);
+  FTG_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int ftg_rowdot_loss(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
+                               const float* rowscale, float* loss_out, ftg_stream_t stream) {
+  k_rowdot<<<1, 1024, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, out, rowscale, loss_out);
   FTG_LAUNCH_CHECK();
   return 0;
 }
 
 // -------------------------------------------------------------------- colsum
-// blockDim = (32, 8): 32 columns per block, rows strided over y; deterministic tree.
-__global__ void k_colsum(const float* __restrict__ a, int lda, int M, int N, const float* __restrict__ rowscale,
-                         float* out, int accumulate) {
-  __shared__ float part[8][33];
+// blockDim = (32, 32): 32 columns per block, rows strided over y; deterministic tree.
+__global__ void __launch_bounds__(1024) k_colsum(const float* __restrict__ a, int lda, int M, int N,
+                                                 const float* __restrict__ rowscale, float* out, int accumulate) {
+  __shared__ float part[32][33];
   int n = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
   if (n < N)
-    for (int m = threadIdx.y; m < M; m += 8) s += a[(size_t)m * lda + n] * (rowscale ? rowscale[m] : 1.f);
+    for (int m = threadIdx.y; m < M; m += 32) s += a[(size_t)m * lda + n] * (rowscale ? rowscale[m] : 1.f);
   part[threadIdx.y][threadIdx.x] = s;
   __syncthreads();
   if (threadIdx.y == 0 && n < N) {
     float t = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) t += part[j][threadIdx.x];
+    for (int j = 0; j < 32; ++j) t += part[j][threadIdx.x];
     out[n] = accumulate ? out[n] + t : t;
   }
 }
 
 extern "C" int ftg_colsum(const float* a, int lda, int M, int N, const float* rowscale, float* out, int accumulate,
                           ftg_stream_t stream) {
-  k_colsum<<<ftg_cdiv(N, 32), dim3(32, 8), 0, (cudaStream_t)stream>>>(a, lda, M, N, rowscale, out, accumulate);
+  k_colsum<<<ftg_cdiv(N, 32), dim3(32, 32), 0, (cudaStream_t)stream>>>(a, lda, M, N, rowscale, out, accumulate);
   FTG_LAUNCH_CHECK();
   return 0;
 }
@@ -239,65 +258,69 @@ extern "C" int ftg_scale_outer_mask(const float* rowscale, const float* v, const
 }
 
 // --------------------------------------------------------------- bn_relu_fwd
-// blockDim = (32, 16): 32 features per block; two-pass batch statistics in fp32.
-__global__ void k_bn_relu_fwd(const float* __restrict__ a, int lda, int B, int H, const float* __restrict__ gamma,
-                              const float* __restrict__ beta, float* running_mean, float* running_var, float* out,
-                              int ldo, float* save_mean, float* save_invstd, int training, float eps, float momentum,
-                              float* nbt) {
-  __shared__ float red[16][33];
-  __shared__ float s_mean[32], s_inv[32];
-  int h = blockIdx.x * 32 + threadIdx.x;
-  bool ok = h < H;
-  if (training) {
-    float s = 0.f;
-    if (ok)
-      for (int m = threadIdx.y; m < B; m += 16) s += a[(size_t)m * lda + h];
-    red[threadIdx.y][threadIdx.x] = s;
-    __syncthreads();
-    if (threadIdx.y == 0) {
-      float t = 0.f;
+// blockDim = (8, 128): 8 features per block (one 32 B sector per row), 128 row lanes, so a
+// 256-wide layer fills 32 CTAs with 4 rows per thread; two-pass batch statistics in fp32.
+#define BN_F 8
+#define BN_R 128
+__device__ __forceinline__ float bn_block_reduce(float v, float (*red)[BN_F], int tx, int ty) {
+  // reduce over ty (128 lanes = 4 warps of 32 threads; a warp holds 4 rows x 8 features)
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 16);
+  __syncthreads();
+  if ((ty & 3) == 0) red[ty >> 2][tx] = v;
+  __syncthreads();
+  float t = 0.f;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) t += red[j][threadIdx.x];
-      s_mean[threadIdx.x] = t / B;
-    }
-    __syncthreads();
-    float mu = s_mean[threadIdx.x];
-    float q = 0.f;
-    if (ok)
-      for (int m = threadIdx.y; m < B; m += 16) {
-        float d = a[(size_t)m * lda + h] - mu;
-        q += d * d;
-      }
-    red[threadIdx.y][threadIdx.x] = q;
-    __syncthreads();
-    if (threadIdx.y == 0) {
-      float t = 0.f;
+  for (int j = 0; j < BN_R / 4; ++j) t += red[j][tx];
+  return t;
+}
+
+__global__ void __launch_bounds__(BN_F * BN_R)
+k_bn_relu_fwd(const float* __restrict__ a, int lda, int B, int H, const float* __restrict__ gamma,
+              const float* __restrict__ beta, float* running_mean, float* running_var, float* out, int ldo,
+              float* save_mean, float* save_invstd, float eps, float momentum, float* nbt) {
+  __shared__ float red[BN_R / 4][BN_F];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int h = blockIdx.x * BN_F + tx;
+  const bool ok = h < H;
+  // rows ty, ty+128, ... : the first 8 per thread stay in registers (B <= 1024 never re-reads)
+  float x[8];
+  float s = 0.f;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) t += red[j][threadIdx.x];
-      float var = t / B;
-      s_inv[threadIdx.x] = rsqrtf(var + eps);
-      if (ok) {
-        running_mean[h] = (1.f - momentum) * running_mean[h] + momentum * mu;
-        float unbiased = var * ((float)B / (float)max(B - 1, 1));
-        running_var[h] = (1.f - momentum) * running_var[h] + momentum * unbiased;
-        if (save_mean) { save_mean[h] = mu; save_invstd[h] = s_inv[threadIdx.x]; }
-      }
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0 && threadIdx.y == 0 && nbt) nbt[0] += 1.f;
-    __syncthreads();
-  } else {
-    if (threadIdx.y == 0 && ok) {
-      s_mean[threadIdx.x] = running_mean[h];
-      s_inv[threadIdx.x] = rsqrtf(running_var[h] + eps);
-    }
-    __syncthreads();
+  for (int i = 0; i < 8; ++i) {
+    const int m = ty + i * BN_R;
+    x[i] = (ok && m < B) ? a[(size_t)m * lda + h] : 0.f;
+    s += x[i];
   }
+  for (int m = ty + 8 * BN_R; m < B; m += BN_R) s += ok ? a[(size_t)m * lda + h] : 0.f;
+  const float mu = bn_block_reduce(s, red, tx, ty) / (float)B;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float d = x[i] - mu;
+    if (ty + i * BN_R < B) q += d * d;
+  }
+  for (int m = ty + 8 * BN_R; m < B; m += BN_R) {
+    const float d = (ok ? a[(size_t)m * lda + h] : 0.f) - mu;
+    q += d * d;
+  }
+  const float var = bn_block_reduce(q, red, tx, ty) / (float)B;
+  const float inv = rsqrtf(var + eps);
+  if (ty == 0 && ok) {
+    running_mean[h] = (1.f - momentum) * running_mean[h] + momentum * mu;
+    running_var[h] = (1.f - momentum) * running_var[h] + momentum * var * ((float)B / (float)max(B - 1, 1));
+    if (save_mean) { save_mean[h] = mu; save_invstd[h] = inv; }
+  }
+  if (blockIdx.x == 0 && tx == 0 && ty == 0 && nbt) nbt[0] += 1.f;
   if (!ok) return;
-  float mu = s_mean[threadIdx.x], inv = s_inv[threadIdx.x], g = gamma[h], b = beta[h];
-  for (int m = threadIdx.y; m < B; m += 16) {
-    float y = (a[(size_t)m * lda + h] - mu) * inv * g + b;
-    out[(size_t)m * ldo + h] = fmaxf(y, 0.f);
+  const float g = gamma[h], b = beta[h];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int m = ty + i * BN_R;
+    if (m < B) out[(size_t)m * ldo + h] = fmaxf((x[i] - mu) * inv * g + b, 0.f);
   }
+  for (int m = ty + 8 * BN_R; m < B; m += BN_R)
+    out[(size_t)m * ldo + h] = fmaxf((a[(size_t)m * lda + h] - mu) * inv * g + b, 0.f);
 }
 
 // eval mode is row independent: tile rows over blockIdx.y so 40 000-row generation fills the GPU
@@ -320,8 +343,8 @@ extern "C" int ftg_bn_relu_fwd(const float* a, int lda, int B, int H, const floa
                                float* save_invstd, int training, float eps, float momentum,
                                float* num_batches_tracked, ftg_stream_t stream) {
   if (training) {
-    k_bn_relu_fwd<<<ftg_cdiv(H, 32), dim3(32, 16), 0, (cudaStream_t)stream>>>(
-        a, lda, B, H, gamma, beta, running_mean, running_var, out, ldo, save_mean, save_invstd, 1, eps, momentum,
+    k_bn_relu_fwd<<<ftg_cdiv(H, BN_F), dim3(BN_F, BN_R), 0, (cudaStream_t)stream>>>(
+        a, lda, B, H, gamma, beta, running_mean, running_var, out, ldo, save_mean, save_invstd, eps, momentum,
         num_batches_tracked);
   } else {
     k_bn_relu_eval<<<dim3(ftg_cdiv(H, 32), ftg_cdiv(B, 128)), dim3(32, 8), 0, (cudaStream_t)stream>>>(
@@ -332,42 +355,61 @@ extern "C" int ftg_bn_relu_fwd(const float* a, int lda, int B, int H, const floa
 }
 
 // --------------------------------------------------------------- bn_relu_bwd
-__global__ void k_bn_relu_bwd(const float* __restrict__ dout, int lddo, const float* __restrict__ a, int lda, int B,
-                              int H, const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
-                              const float* __restrict__ gamma, const float* __restrict__ beta, float* da, int ldda,
-                              float* dgamma, float* dbeta) {
-  __shared__ float red0[16][33], red1[16][33];
-  __shared__ float s_db[32], s_dg[32];
-  int h = blockIdx.x * 32 + threadIdx.x;
-  bool ok = h < H;
-  float mu = ok ? save_mean[h] : 0.f, inv = ok ? save_invstd[h] : 0.f, g = ok ? gamma[h] : 0.f, b = ok ? beta[h] : 0.f;
+// Also emits d(fc bias) = column sum of `da` (the Linear in front of the BatchNorm), so the
+// generator backward needs no separate reduction kernel.
+__global__ void __launch_bounds__(BN_F * BN_R)
+k_bn_relu_bwd(const float* __restrict__ dout, int lddo, const float* __restrict__ a, int lda, int B, int H,
+              const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+              const float* __restrict__ gamma, const float* __restrict__ beta, float* da, int ldda, float* dgamma,
+              float* dbeta, float* dbias_fc) {
+  __shared__ float red[BN_R / 4][BN_F];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int h = blockIdx.x * BN_F + tx;
+  const bool ok = h < H;
+  const float mu = ok ? save_mean[h] : 0.f, inv = ok ? save_invstd[h] : 0.f, g = ok ? gamma[h] : 0.f,
+              b = ok ? beta[h] : 0.f;
+  float xh[8], dy[8];
   float sb = 0.f, sg = 0.f;
-  if (ok)
-    for (int m = threadIdx.y; m < B; m += 16) {
-      float xh = (a[(size_t)m * lda + h] - mu) * inv;
-      float dy = (xh * g + b > 0.f) ? dout[(size_t)m * lddo + h] : 0.f;
-      sb += dy;
-      sg += dy * xh;
-    }
-  red0[threadIdx.y][threadIdx.x] = sb;
-  red1[threadIdx.y][threadIdx.x] = sg;
-  __syncthreads();
-  if (threadIdx.y == 0) {
-    float t0 = 0.f, t1 = 0.f;
 #pragma unroll
-    for (int j = 0; j < 16; ++j) { t0 += red0[j][threadIdx.x]; t1 += red1[j][threadIdx.x]; }
-    s_db[threadIdx.x] = t0;
-    s_dg[threadIdx.x] = t1;
-    if (ok) { dbeta[h] = t0; dgamma[h] = t1; }
+  for (int i = 0; i < 8; ++i) {
+    const int m = ty + i * BN_R;
+    const bool in = ok && m < B;
+    xh[i] = in ? (a[(size_t)m * lda + h] - mu) * inv : 0.f;
+    dy[i] = (in && xh[i] * g + b > 0.f) ? dout[(size_t)m * lddo + h] : 0.f;
+    sb += dy[i];
+    sg += dy[i] * xh[i];
   }
-  __syncthreads();
-  if (!ok) return;
-  float db = s_db[threadIdx.x], dg = s_dg[threadIdx.x];
-  float scale = g * inv / (float)B;
-  for (int m = threadIdx.y; m < B; m += 16) {
-    float xh = (a[(size_t)m * lda + h] - mu) * inv;
-    float dy = (xh * g + b > 0.f) ? dout[(size_t)m * lddo + h] : 0.f;
-    da[(size_t)m * ldda + h] = scale * ((float)B * dy - db - xh * dg);
+  for (int m = ty + 8 * BN_R; m < B; m += BN_R) {
+    const float x = ok ? (a[(size_t)m * lda + h] - mu) * inv : 0.f;
+    const float d = (ok && x * g + b > 0.f) ? dout[(size_t)m * lddo + h] : 0.f;
+    sb += d;
+    sg += d * x;
+  }
+  const float db = bn_block_reduce(sb, red, tx, ty);
+  const float dg = bn_block_reduce(sg, red, tx, ty);
+  if (ty == 0 && ok) { dbeta[h] = db; dgamma[h] = dg; }
+  const float scale = g * inv / (float)B;
+  float sda = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int m = ty + i * BN_R;
+    if (ok && m < B) {
+      const float v = scale * ((float)B * dy[i] - db - xh[i] * dg);
+      da[(size_t)m * ldda + h] = v;
+      sda += v;
+    }
+  }
+  for (int m = ty + 8 * BN_R; m < B; m += BN_R) {
+    if (!ok) continue;
+    const float x = (a[(size_t)m * lda + h] - mu) * inv;
+    const float d = (x * g + b > 0.f) ? dout[(size_t)m * lddo + h] : 0.f;
+    const float v = scale * ((float)B * d - db - x * dg);
+    da[(size_t)m * ldda + h] = v;
+    sda += v;
+  }
+  if (dbias_fc) {
+    const float t = bn_block_reduce(sda, red, tx, ty);
+    if (ty == 0 && ok) dbias_fc[h] = t;
   }
 }
 
@@ -375,69 +417,83 @@ extern "C" int ftg_bn_relu_bwd(const float* dout, int lddo, const float* a, int 
                                const float* save_mean, const float* save_invstd, const float* gamma,
                                const float* beta, float* da, int ldda, float* dgamma, float* dbeta,
                                ftg_stream_t stream) {
-  k_bn_relu_bwd<<<ftg_cdiv(H, 32), dim3(32, 16), 0, (cudaStream_t)stream>>>(dout, lddo, a, lda, B, H, save_mean,
-                                                                            save_invstd, gamma, beta, da, ldda,
-                                                                            dgamma, dbeta);
+  k_bn_relu_bwd<<<ftg_cdiv(H, BN_F), dim3(BN_F, BN_R), 0, (cudaStream_t)stream>>>(
+      dout, lddo, a, lda, B, H, save_mean, save_invstd, gamma, beta, da, ldda, dgamma, dbeta, nullptr);
+  FTG_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int ftg_bn_relu_bwd_bias(const float* dout, int lddo, const float* a, int lda, int B, int H,
+                                    const float* save_mean, const float* save_invstd, const float* gamma,
+                                    const float* beta, float* da, int ldda, float* dgamma, float* dbeta,
+                                    float* dbias_fc, ftg_stream_t stream) {
+  k_bn_relu_bwd<<<ftg_cdiv(H, BN_F), dim3(BN_F, BN_R), 0, (cudaStream_t)stream>>>(
+      dout, lddo, a, lda, B, H, save_mean, save_invstd, gamma, beta, da, ldda, dgamma, dbeta, dbias_fc);
   FTG_LAUNCH_CHECK();
   return 0;
 }
 
 // -------------------------------------------------------------- activate_fwd
-// One thread per (row, span): tanh spans are 1 wide, softmax spans a handful of options.
-__global__ void k_activate_fwd(const float* __restrict__ fake, int ldf, int B, int dd, int n_spans,
-                               const int* __restrict__ span_start, const int* __restrict__ span_width,
-                               const int* __restrict__ span_kind, float* out, int ldo, float inv_tau, const float* u,
-                               int ldu, const int64_t* state, int stream_id, const float* cond, int ldc, int n_opt,
-                               int use_noise) {
-  long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  long long n_work = (long long)B * n_spans;
-  if (t < n_work) {
-    int row = (int)(t / n_spans), s = (int)(t % n_spans);
-    int st = span_start[s], w = span_width[s];
-    const float* x = fake + (size_t)row * ldf + st;
-    float* o = out + (size_t)row * ldo + st;
+// One CTA per row.  Phase 1: every column computes tanh or the tempered, gumbel-perturbed
+// logit into shared memory.  Phase 2: one thread per softmax span finds max / sum.
+// Phase 3: every column normalises.  The conditional vector is appended by the same CTA
+// (this is the torch.cat([fakeact, c1]) of the reference written in place).
+__global__ void __launch_bounds__(128)
+k_activate_fwd(const float* __restrict__ fake, int ldf, int dd, int n_spans, const int* __restrict__ span_start,
+               const int* __restrict__ span_width, const int* __restrict__ span_kind,
+               const int* __restrict__ col_span, float* out, int ldo, float inv_tau, const float* u, int ldu,
+               const int64_t* state, int stream_id, const float* cond, int ldc, int n_opt, int use_noise) {
+  extern __shared__ float sm[];
+  float* val = sm;                 // [dd]
+  float* smax = sm + dd;           // [n_spans]
+  float* sinv = smax + n_spans;    // [n_spans]
+  const int row = blockIdx.x;
+  const float* x = fake + (size_t)row * ldf;
+  float* o = out + (size_t)row * ldo;
+  for (int j = threadIdx.x; j < dd; j += blockDim.x) {
+    const int s = col_span[j];
     if (span_kind[s] == 0) {
-      for (int j = 0; j < w; ++j) o[j] = tanhf(x[j]);
+      val[j] = tanhf(x[j]);
     } else {
-      float mx = -3.0e38f;
-      for (int j = 0; j < w; ++j) {
-        float g = 0.f;
-        if (use_noise) {
-          float uu = u ? u[(size_t)row * ldu + st + j] : philox_uniform(state, stream_id, (uint32_t)(row * dd + st + j));
-          uu = fminf(fmaxf(uu, 1e-10f), 1.0f - 1e-7f);
-          g = -logf(-logf(uu));
-        }
-        float v = (x[j] + g) * inv_tau;
-        o[j] = v;
-        mx = fmaxf(mx, v);
+      float g = 0.f;
+      if (use_noise) {
+        float uu = u ? u[(size_t)row * ldu + j] : philox_uniform(state, stream_id, (uint32_t)(row * dd + j));
+        uu = fminf(fmaxf(uu, 1e-10f), 1.0f - 1e-7f);
+        g = -logf(-logf(uu));
       }
-      float sum = 0.f;
-      for (int j = 0; j < w; ++j) {
-        float e = expf(o[j] - mx);
-        o[j] = e;
-        sum += e;
-      }
-      float inv = 1.f / sum;
-      for (int j = 0; j < w; ++j) o[j] *= inv;
+      val[j] = (x[j] + g) * inv_tau;
     }
   }
-  if (cond) {
-    long long total = (long long)B * n_opt;
-    for (long long e = t; e < total; e += (long long)gridDim.x * blockDim.x) {
-      int row = (int)(e / n_opt), j = (int)(e % n_opt);
-      out[(size_t)row * ldo + dd + j] = cond[(size_t)row * ldc + j];
-    }
+  __syncthreads();
+  for (int s = threadIdx.x; s < n_spans; s += blockDim.x) {
+    if (span_kind[s] == 0) continue;
+    const int st = span_start[s], w = span_width[s];
+    float mx = -3.0e38f;
+    for (int k = 0; k < w; ++k) mx = fmaxf(mx, val[st + k]);
+    float sum = 0.f;
+    for (int k = 0; k < w; ++k) sum += expf(val[st + k] - mx);
+    smax[s] = mx;
+    sinv[s] = 1.f / sum;
   }
+  __syncthreads();
+  for (int j = threadIdx.x; j < dd; j += blockDim.x) {
+    const int s = col_span[j];
+    o[j] = (span_kind[s] == 0) ? val[j] : expf(val[j] - smax[s]) * sinv[s];
+  }
+  if (cond)
+    for (int j = threadIdx.x; j < n_opt; j += blockDim.x) o[dd + j] = cond[(size_t)row * ldc + j];
 }
 
 extern "C" int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n_spans, const int* span_start,
-                                const int* span_width, const int* span_kind, float* out, int ldo, float tau,
-                                const float* u, int ldu, const int64_t* rng_state, int rng_stream, const float* cond,
-                                int ldc, int n_opt, int use_noise, ftg_stream_t stream) {
-  long long n_work = (long long)B * n_spans;
-  k_activate_fwd<<<ftg_cdiv(n_work, 128), 128, 0, (cudaStream_t)stream>>>(
-      fake, ldf, B, dd, n_spans, span_start, span_width, span_kind, out, ldo, 1.f / tau, u, ldu, rng_state, rng_stream,
-      cond, ldc, n_opt, use_noise);
+                                const int* span_width, const int* span_kind, const int* col_span, float* out,
+                                int ldo, float tau, const float* u, int ldu, const int64_t* rng_state,
+                                int rng_stream, const float* cond, int ldc, int n_opt, int use_noise,
+                                ftg_stream_t stream) {
+  size_t smem = (size_t)(dd + 2 * n_spans) * sizeof(float);
+  if (smem > 48 * 1024) return FTG_ERR_UNSUPPORTED;
+  k_activate_fwd<<<B, 128, smem, (cudaStream_t)stream>>>(fake, ldf, dd, n_spans, span_start, span_width, span_kind,
+                                                         col_span, out, ldo, 1.f / tau, u, ldu, rng_state, rng_stream,
+                                                         cond, ldc, n_opt, use_noise);
   FTG_LAUNCH_CHECK();
   return 0;
 }

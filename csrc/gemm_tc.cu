@@ -3,7 +3,8 @@
 //   D[M,N] (+)= epilogue( A[M,K] . B[N,K]^T )      (epilogue: common.cuh::ftg_epilogue_store)
 //
 // * operands are fp32 in global memory; TMA (cp.async.bulk.tensor.2d, SWIZZLE_128B) stages
-//   them into shared memory, the tensor core reads them as tf32, the accumulator tile
+//   them into shared memory (K-major: SWIZZLE_128B; MN-major: SWIZZLE_128B_ATOM_32B, the
+//   only layout tf32 accepts for transposed operands), the tensor core reads them as tf32, the accumulator tile
 //   (128 lanes x 64 columns fp32) lives in TMEM and is read back with tcgen05.ld;
 // * both operand majors are supported natively (K-major: [rows, K]; MN-major: [K, rows]),
 //   so forward (X.W^T), dgrad (dY.W) and wgrad (dY^T.X) need no transposed copies;
@@ -80,15 +81,18 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
       : "memory");
 }
 
-// Shared-memory matrix descriptor (SWIZZLE_128B, sm_100 descriptor version 1).
-//   bits [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout=2
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// Shared-memory matrix descriptor (sm_100 descriptor version 1).
+//   bits [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout
+//   layout 2 = SWIZZLE_128B (16 B atomicity)   : K-major operands
+//   layout 1 = SWIZZLE_128B with 32 B atomicity : the only legal layout for MN-major tf32
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                              uint32_t layout) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)layout << 61;
   return d;
 }
 
@@ -164,10 +168,11 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
 #pragma unroll
       for (int ks = 0; ks < BK / 8; ++ks) {
-        // K-major: 8 tf32 = 32 B step inside the 128 B swizzle row; SBO = 8 rows * 128 B
-        // MN-major: 8 k-rows = 1024 B step; LBO = next 32-element MN chunk, SBO = next 8-k group
-        uint64_t ad = A_MN ? make_desc(sa + ks * 1024, BK * 128, 1024) : make_desc(sa + ks * 32, 16, 1024);
-        uint64_t bd = B_MN ? make_desc(sb + ks * 1024, BK * 128, 1024) : make_desc(sb + ks * 32, 16, 1024);
+        // K-major : 8 tf32 = 32 B step inside the 128 B swizzle row; SBO = 8 rows * 128 B
+        // MN-major: one MMA (K = 8) spans two 4-row swizzle atoms (SBO = 512 B apart); the next
+        //           32-element MN chunk is the next TMA box (LBO = BK * 128 B); 8 k-rows = 1024 B step
+        uint64_t ad = A_MN ? make_desc(sa + ks * 1024, BK * 128, 512, 1) : make_desc(sa + ks * 32, 16, 1024, 2);
+        uint64_t bd = B_MN ? make_desc(sb + ks * 1024, BK * 128, 512, 1) : make_desc(sb + ks * 32, 16, 1024, 2);
         umma_tf32(tmem_base, ad, bd, idesc, (kb > kb0 || ks > 0) ? 1u : 0u);
       }
       umma_commit(empty_bar(s));                // frees the smem slot when these MMAs retire
@@ -186,51 +191,76 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     tmem_ld32(taddr, r);
     tmem_ld32(taddr + 32, r + 32);
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-    if (split_k == 1) {
-      if (m < p.M) {
+    // Stage the accumulator tile through shared memory (the operand ring is idle once the
+    // last MMA has retired) so that global traffic is row-contiguous and the epilogue is a
+    // compact loop instead of 64 unrolled copies of the fused epilogue (I-cache!).
+    constexpr int SLD = BN + 1;
+    float* stage = reinterpret_cast<float*>(gen_base);
+    {
+      float* myrow = stage + row_in_tile * SLD;
 #pragma unroll
-        for (int j = 0; j < BN; ++j) {
-          int n = n0 + j;
-          if (n < p.N) ftg_epilogue_store(p, m, n, __uint_as_float(r[j]));
-        }
-      }
-    } else {
+      for (int j = 0; j < BN; ++j) myrow[j] = __uint_as_float(r[j]);
+    }
+    __syncwarp();
+    const int rows_here = min(32, p.M - (m0 + q * 32));      // rows of this warp's quadrant inside M
+    bool do_epilogue = true;
+    if (split_k > 1) {
+      // ---- split-K: publish the partial tile, last-arriving CTA reduces all partials
       const int tile = blockIdx.y * gridDim.x + blockIdx.x;
       const int n_tiles = gridDim.x * gridDim.y;
-      float* ws = workspace + ((size_t)z * n_tiles + tile) * (BM * BN) + (size_t)row_in_tile * BN;
+      const int et = threadIdx.x - 64;                         // 0..127 among the epilogue threads
+      asm volatile("bar.sync 1, 128;" ::: "memory");           // whole tile staged
+      float4* ws4 = reinterpret_cast<float4*>(workspace + ((size_t)z * n_tiles + tile) * (BM * BN));
 #pragma unroll
-      for (int j = 0; j < BN; j += 4)
-        *reinterpret_cast<float4*>(ws + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
-                                                          __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+      for (int it = 0; it < (BM * BN / 4) / 128; ++it) {       // 16 coalesced float4 per thread
+        const int f = it * 128 + et, row = f / (BN / 4), c4 = f % (BN / 4);
+        const float* sp = stage + row * SLD + c4 * 4;
+        ws4[f] = make_float4(sp[0], sp[1], sp[2], sp[3]);
+      }
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (threadIdx.x == 64) {
+      if (et == 0) {
         int old = atomicAdd(&tile_counters[tile], 1);
         *last_flag = (old == split_k - 1) ? 1 : 0;
-        if (old == split_k - 1) tile_counters[tile] = 0;   // re-arm for the next launch
+        if (old == split_k - 1) tile_counters[tile] = 0;       // re-arm for the next launch
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (*last_flag) {
+      do_epilogue = (*last_flag != 0);
+      if (do_epilogue) {
         __threadfence();
-        if (m < p.M) {
-          const float* wsr = workspace + (size_t)tile * (BM * BN) + (size_t)row_in_tile * BN;
-          const size_t zstride = (size_t)n_tiles * (BM * BN);
-#pragma unroll 4
-          for (int j = 0; j < BN; j += 4) {
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int zz = 0; zz < split_k; ++zz) {
-              float4 v = __ldcg(reinterpret_cast<const float4*>(wsr + zz * zstride + j));
-              acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-            }
-            int n = n0 + j;
-            if (n < p.N) ftg_epilogue_store(p, m, n, acc.x);
-            if (n + 1 < p.N) ftg_epilogue_store(p, m, n + 1, acc.y);
-            if (n + 2 < p.N) ftg_epilogue_store(p, m, n + 2, acc.z);
-            if (n + 3 < p.N) ftg_epilogue_store(p, m, n + 3, acc.w);
+        const size_t zstride4 = (size_t)n_tiles * (BM * BN / 4);
+        const float4* wst4 = reinterpret_cast<const float4*>(workspace + (size_t)tile * (BM * BN));
+        float4 acc[16];
+#pragma unroll
+        for (int it = 0; it < 16; ++it) acc[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int zz = 0; zz < split_k; ++zz) {                 // fixed order => deterministic
+#pragma unroll
+          for (int it = 0; it < 16; ++it) {                    // 16 independent 16 B loads in flight
+            const float4 v = __ldcg(wst4 + zz * zstride4 + it * 128 + et);
+            acc[it].x += v.x; acc[it].y += v.y; acc[it].z += v.z; acc[it].w += v.w;
           }
+        }
+#pragma unroll
+        for (int it = 0; it < 16; ++it) {
+          const int f = it * 128 + et, row = f / (BN / 4), c4 = f % (BN / 4);
+          float* sp = stage + row * SLD + c4 * 4;
+          sp[0] = acc[it].x; sp[1] = acc[it].y; sp[2] = acc[it].z; sp[3] = acc[it].w;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+    }
+    if (do_epilogue) {
+      for (int rr = 0; rr < rows_here; ++rr) {
+        const float* srow = stage + (q * 32 + rr) * SLD;
+        const int mm = m0 + q * 32 + rr;
+#pragma unroll
+        for (int half = 0; half < BN / 32; ++half) {
+          const int n = n0 + lane + 32 * half;
+          if (n < p.N) ftg_epilogue_store(p, mm, n, srow[lane + 32 * half]);
         }
       }
     }
+    (void)m;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -259,7 +289,8 @@ EncodeTiledFn get_encode() {
 }
 
 // 2-D fp32 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld floats.
-bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, int box_inner, int box_outer) {
+bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, int box_inner, int box_outer,
+              bool mn_major) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return false;
   cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
@@ -267,7 +298,9 @@ bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, 
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
 }
@@ -320,8 +353,8 @@ extern "C" int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* worksp
   if (split_k > nkb) split_k = nkb;
   if (split_k > 1 && (!workspace || !tile_counters)) return FTG_ERR_UNSUPPORTED;
   CUtensorMap ma, mb;
-  bool ok = p.a_t ? make_map(&ma, p.a, p.M, p.K, p.lda, 32, BK) : make_map(&ma, p.a, p.K, p.M, p.lda, BK, BM);
-  ok = ok && (p.b_t ? make_map(&mb, p.b, p.N, p.K, p.ldb, 32, BK) : make_map(&mb, p.b, p.K, p.N, p.ldb, BK, BN));
+  bool ok = p.a_t ? make_map(&ma, p.a, p.M, p.K, p.lda, 32, BK, true) : make_map(&ma, p.a, p.K, p.M, p.lda, BK, BM, false);
+  ok = ok && (p.b_t ? make_map(&mb, p.b, p.N, p.K, p.ldb, 32, BK, true) : make_map(&mb, p.b, p.K, p.N, p.ldb, BK, BN, false));
   if (!ok) return FTG_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
   if (p.a_t) return p.b_t ? launch<true, true>(ma, mb, p, split_k, workspace, tile_counters, s)

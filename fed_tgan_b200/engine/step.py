@@ -111,6 +111,9 @@ class TrainEngine:
         rs[Bp:2 * Bp] = -1.0 / Bp
         rs[2 * Bp:] = 1.0
         self.rowscale_d = rs
+        rl = rs.clone()
+        rl[2 * Bp:] = 0.0           # interpolated rows do not enter the WGAN loss value
+        self.rowscale_loss = rl
         self.rowscale_g = torch.full((Bp,), -1.0 / Bp, **f32)
         self.alpha = torch.zeros(B, **f32)
         # ---- scalars (device resident; read back only on request)
@@ -144,6 +147,8 @@ class TrainEngine:
         t = self.table
         h0 = self.off[0]
         rng = self.rng
+        if inject is None and self.device.type == "cuda" and ops.native_available() and not ops._force_reference():
+            return self._prep_fused(with_real)
         R = lambda k: self._rand(inject, k, None)  # noqa: E731
         ops.fill_normal(self.h[:, h0:h0 + E], z=R(f"z_{prefix}"), rng=rng, stream=S_Z_D if with_real else S_Z_G)
         ops.sample_condvec(t.cum_p, self.tables["soft_width"], self.col, self.opt,
@@ -160,6 +165,19 @@ class TrainEngine:
             dd = self.layout.data_dim
             ops.write_condvec(self.col, self.opt, self.tables["soft_cstart"],
                               real[:, dd:dd + self.layout.n_opt], None, self.perm)
+        return c1
+
+    def _prep_fused(self, with_real):
+        from ..ops import native
+
+        B, E, h0 = self.B, self.E, self.off[0]
+        z = self.h[:, h0:h0 + E]
+        c1 = self.h[:, h0 + E:h0 + E + self.layout.n_opt]
+        if with_real:
+            native.prep_d_batch(self.table, self.tables, z, c1, self.X[B:2 * B], self.col, self.opt, self.perm,
+                                self.rid, self.rng, S_Z_D, S_COL_D, S_PERM, S_ROW)
+        else:
+            native.prep_g_batch(self.table, self.tables, z, c1, self.m1, self.col, self.opt, self.rng, S_Z_G, S_COL_G)
         return c1
 
     # --------------------------------------------------------------- generator
@@ -199,18 +217,19 @@ class TrainEngine:
                 dh[:, lo:hi], self.a[l - 1], self.save_mean[l - 1], self.save_invstd[l - 1],
                 self._g(l - 1, "bn.weight"), self._g(l - 1, "bn.bias"), self.da[l - 1],
                 self.G.grad_view(f"seq.{l - 1}.bn.weight"), self.G.grad_view(f"seq.{l - 1}.bn.bias"),
+                dbias_fc=self.G.grad_view(f"seq.{l - 1}.fc.bias"),
             )
             x = self.h[:, hi: self.off[0] + self.d0]
             ops.linear(self.da[l - 1], x, self.G.grad_view(f"seq.{l - 1}.fc.weight"), a_t=True, b_t=True)
-            ops.colsum(self.da[l - 1], self.G.grad_view(f"seq.{l - 1}.fc.bias"))
             if l > 1:
                 width = self.sum_h - hi      # columns of W_l that multiply r_{l-1}..r_1
                 ops.linear(self.da[l - 1], self._gw(l - 1)[:, :width], dh[:, hi: self.sum_h], b_t=True,
                            accumulate=True)
 
     # ------------------------------------------------------------ discriminator
-    def d_forward(self, rows, inject, key, stream):
-        """Forward rows ``[0:rows)`` of the packed batch; fills Lact/Mask/y."""
+    def d_forward(self, rows, inject, key, stream, rowscale=None, loss_out=None):
+        """Forward rows ``[0:rows)`` of the packed batch; fills Lact/Mask/y (and the fused
+        scalar ``loss_out = sum rowscale * y``)."""
         cfg = self.cfg
         x = self.Xp[:rows]
         for l, hl in enumerate(self.dhid):
@@ -222,7 +241,7 @@ class TrainEngine:
                        slope=cfg.leaky_slope, p=cfg.dropout_p)
             x = self.Lact[l][:rows]
         nl = len(self.dhid)
-        ops.rowdot(x, self._dw(nl), self._db(nl), self.y[:rows])
+        ops.rowdot(x, self._dw(nl), self._db(nl), self.y[:rows], rowscale=rowscale, loss_out=loss_out)
 
     def d_signals(self, rows, rowscale):
         """Backward signals ``Z_l = dLoss/d(pre-activation_l)`` for ``loss = sum rowscale*y``."""
@@ -241,9 +260,7 @@ class TrainEngine:
                          rng=self.rng, stream=S_GUMBEL_D, cond=c1)
         ops.slerp(self.X[B:2 * B, :din], self.X[:B, :din], self.X[2 * B:, :din],
                   alpha=self._rand(inject, "alpha", None), rng=self.rng, stream=S_ALPHA)
-        self.d_forward(3 * Bp, inject, "u_drop_d", S_DROP_D)
-        # WGAN loss value
-        ops.colsum(self.y[:2 * Bp].view(-1, 1), self.loss_d, rowscale=self.rowscale_d[:2 * Bp])
+        self.d_forward(3 * Bp, inject, "u_drop_d", S_DROP_D, self.rowscale_loss, self.loss_d)   # + WGAN loss value
         # backward signals for all rows (interp rows carry the d y / d x seed)
         self.d_signals(3 * Bp, self.rowscale_d)
         nl = len(self.dhid)
@@ -275,8 +292,7 @@ class TrainEngine:
         self.g_forward(training=True)
         ops.activate_fwd(self.fake, self.tables, self.X[:B], tau=cfg.tau, u=self._rand(inject, "u_gumbel_g", None),
                          rng=self.rng, stream=S_GUMBEL_G, cond=c1)
-        self.d_forward(Bp, inject, "u_drop_g", S_DROP_G)
-        ops.colsum(self.y[:Bp].view(-1, 1), self.loss_g_adv, rowscale=self.rowscale_g)
+        self.d_forward(Bp, inject, "u_drop_g", S_DROP_G, self.rowscale_g, self.loss_g_adv)
         self.d_signals(Bp, self.rowscale_g)
         ops.linear(self.Z[0][:Bp], self._dw(0), self.dXp, b_t=True)
         ops.activate_bwd(self.dX[:, :dd], self.X[:B, :dd], self.tables, self.dfake, tau=cfg.tau)

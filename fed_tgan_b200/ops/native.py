@@ -58,11 +58,16 @@ _choose_split = _sig("ftg_gemm_tc_choose_split", [_i, _i, _i])
 _ws_bytes = _sig("ftg_gemm_tc_workspace_bytes", [_i, _i, _i], _ll)
 _num_tiles = _sig("ftg_gemm_tc_num_tiles", [_i, _i])
 _rowdot = _sig("ftg_rowdot", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp])
+_rowdot_loss = _sig("ftg_rowdot_loss", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp])
+_prep_select = _sig("ftg_prep_select", [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp])
+_prep_rows = _sig("ftg_prep_rows", [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _vp, _i, _vp,
+                                    _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _i, _vp, _i, _i, _vp])
 _colsum = _sig("ftg_colsum", [_vp, _i, _i, _i, _vp, _vp, _i, _vp])
 _som = _sig("ftg_scale_outer_mask", [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp])
 _bn_fwd = _sig("ftg_bn_relu_fwd", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp])
 _bn_bwd = _sig("ftg_bn_relu_bwd", [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp])
-_act_fwd = _sig("ftg_activate_fwd", [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _f, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp])
+_bn_bwd_bias = _sig("ftg_bn_relu_bwd_bias", [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp])
+_act_fwd = _sig("ftg_activate_fwd", [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _f, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp])
 _act_bwd = _sig("ftg_activate_bwd", [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _f, _i, _vp])
 _cond_loss = _sig("ftg_cond_loss", [_vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp])
 _slerp = _sig("ftg_slerp", [_vp, _i, _vp, _i, _vp, _i, _i, _i, _vp, _vp, _i, _vp])
@@ -206,9 +211,13 @@ def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None
     return out
 
 
-def rowdot(a, w, bias, out):
+def rowdot(a, w, bias, out, rowscale=None, loss_out=None):
     pa, lda = _m(a)
-    _ck(_rowdot(pa, lda, a.shape[0], a.shape[1], _p(w), _p(bias), _p(out), _stream()), "rowdot")
+    if loss_out is not None:
+        _ck(_rowdot_loss(pa, lda, a.shape[0], a.shape[1], _p(w), _p(bias), _p(out), _p(rowscale), _p(loss_out),
+                         _stream()), "rowdot_loss")
+    else:
+        _ck(_rowdot(pa, lda, a.shape[0], a.shape[1], _p(w), _p(bias), _p(out), _stream()), "rowdot")
     return out
 
 
@@ -235,12 +244,16 @@ def bn_relu_fwd(a, gamma, beta, running_mean, running_var, out, save_mean, save_
     return out
 
 
-def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta):
+def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta, dbias_fc=None):
     pd, ldd = _m(dout)
     pa, lda = _m(a)
     pda, ldda = _m(da)
-    _ck(_bn_bwd(pd, ldd, pa, lda, a.shape[0], a.shape[1], _p(save_mean), _p(save_invstd), _p(gamma), _p(beta), pda,
-                ldda, _p(dgamma), _p(dbeta), _stream()), "bn_relu_bwd")
+    if dbias_fc is not None:
+        _ck(_bn_bwd_bias(pd, ldd, pa, lda, a.shape[0], a.shape[1], _p(save_mean), _p(save_invstd), _p(gamma),
+                         _p(beta), pda, ldda, _p(dgamma), _p(dbeta), _p(dbias_fc), _stream()), "bn_relu_bwd_bias")
+    else:
+        _ck(_bn_bwd(pd, ldd, pa, lda, a.shape[0], a.shape[1], _p(save_mean), _p(save_invstd), _p(gamma), _p(beta),
+                    pda, ldda, _p(dgamma), _p(dbeta), _stream()), "bn_relu_bwd")
     return da
 
 
@@ -252,9 +265,9 @@ def activate_fwd(fake, tables, out, *, tau=0.2, u=None, rng=None, stream=0, cond
     pc, ldc = _m(cond)
     n_opt = cond.shape[1] if cond is not None else 0
     _ck(_act_fwd(pf, ldf, fake.shape[0], dd, tables["span_start"].numel(), _p(tables["span_start"]),
-                 _p(tables["span_width"]), _p(tables["span_kind"]), po, ldo, float(tau), pu, ldu,
-                 _p(rng.state) if rng is not None else None, int(stream), pc, ldc, n_opt, int(hard_noise), _stream()),
-        "activate_fwd")
+                 _p(tables["span_width"]), _p(tables["span_kind"]), _p(tables["col_span"]), po, ldo, float(tau), pu,
+                 ldu, _p(rng.state) if rng is not None else None, int(stream), pc, ldc, n_opt, int(hard_noise),
+                 _stream()), "activate_fwd")
     return out
 
 
@@ -353,6 +366,34 @@ def expand_rows(vals, codes, rid, tables, out):
     _ck(_expand_rows(_p(vals), vals.shape[1], _p(codes), codes.shape[1], _p(rid), _p(tables["tanh_start"]),
                      _p(tables["soft_start"]), po, ldo, dd, out.shape[0], _stream()), "expand_rows")
     return out
+
+
+def prep_g_batch(table, tables, z_out, c_out, m_out, col, opt, rng, s_z, s_col):
+    """Fused G-step preparation: (col, opt) draw, z ~ N(0,1), one-hot c1, column mask m1."""
+    pz, ldz = _m(z_out)
+    pc, ldc = _m(c_out)
+    pm, ldm = _m(m_out)
+    _ck(_prep_rows(0, _p(col), _p(opt), None, None, _p(tables["soft_cstart"]), pz, ldz, z_out.shape[1], pc, ldc,
+                   c_out.shape[1], pm, ldm, m_out.shape[1], None, 0, None, None, None, None, 0, 0,
+                   _p(table.cum_p), table.cum_p.shape[1], _p(tables["soft_width"]), z_out.shape[0], _p(rng.state),
+                   int(s_z), int(s_col), _stream()), "prep_rows(G)")
+
+
+def prep_d_batch(table, tables, z_out, c_out, real_out, col, opt, perm, rid, rng, s_z, s_col, s_perm, s_row):
+    """Fused D-step preparation: select kernel + per-row writer (z, c1, real row | c2)."""
+    B = z_out.shape[0]
+    dd = tables["col_span"].numel()
+    _ck(_prep_select(_p(table.cum_p), table.cum_p.shape[0], table.cum_p.shape[1], _p(tables["soft_width"]),
+                     _p(tables["soft_cstart"]), _p(table.row_ptr), _p(table.row_ids), _p(col), _p(opt), _p(perm),
+                     _p(rid), B, _p(rng.state), int(s_col), int(s_perm), int(s_row), _stream()), "prep_select")
+    pz, ldz = _m(z_out)
+    pc, ldc = _m(c_out)
+    pr, ldr = _m(real_out)
+    _ck(_prep_rows(1, _p(col), _p(opt), _p(perm), _p(rid), _p(tables["soft_cstart"]), pz, ldz, z_out.shape[1], pc,
+                   ldc, c_out.shape[1], None, 0, table.cum_p.shape[0], _p(table.vals), table.vals.shape[1],
+                   _p(table.codes), _p(tables["tanh_start"]), _p(tables["soft_start"]), pr, ldr, dd,
+                   _p(table.cum_p), table.cum_p.shape[1], _p(tables["soft_width"]), B, _p(rng.state), int(s_z),
+                   int(s_col), _stream()), "prep_rows(D)")
 
 
 _decode_cache = {}

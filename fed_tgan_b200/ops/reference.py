@@ -86,9 +86,12 @@ def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None
     return out
 
 
-def rowdot(a, w, bias, out):
-    """``out[m] = a[m,:] . w + bias`` (the discriminator's 1-wide head)."""
+def rowdot(a, w, bias, out, rowscale=None, loss_out=None):
+    """``out[m] = a[m,:] . w + bias`` (the discriminator's 1-wide head); optionally also
+    ``loss_out = sum_m rowscale[m] * out[m]``."""
     out.copy_(a @ w.reshape(-1) + (bias.reshape(()) if bias is not None else 0.0))
+    if loss_out is not None:
+        loss_out.copy_((out * rowscale).sum().reshape(1))
     return out
 
 
@@ -131,8 +134,9 @@ def bn_relu_fwd(a, gamma, beta, running_mean, running_var, out, save_mean, save_
     return out
 
 
-def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta):
-    """Backward of ``relu(bn_train(a))``.  ``dgamma``/``dbeta`` are overwritten."""
+def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta, dbias_fc=None):
+    """Backward of ``relu(bn_train(a))``.  ``dgamma``/``dbeta`` are overwritten; ``dbias_fc``
+    (optional) receives the column sum of ``da`` = gradient of the preceding Linear's bias."""
     n = a.shape[0]
     xhat = (a - save_mean) * save_invstd
     dy = dout * ((xhat * gamma + beta) > 0).to(a.dtype)
@@ -141,6 +145,8 @@ def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta)
     da.copy_(gamma * save_invstd / n * (n * dy - db - xhat * dg))
     dgamma.copy_(dg)
     dbeta.copy_(db)
+    if dbias_fc is not None:
+        dbias_fc.copy_(da.sum(0))
     return da
 
 

@@ -59,6 +59,9 @@ int ftg_gemm_tc_num_tiles(int M, int N);
 /* ---- small dense helpers ------------------------------------------------ */
 int ftg_rowdot(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
                ftg_stream_t stream);
+/* rowdot + fused scalar  loss_out = sum_m rowscale[m] * out[m]  (WGAN loss value) */
+int ftg_rowdot_loss(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
+                    const float* rowscale, float* loss_out, ftg_stream_t stream);
 int ftg_colsum(const float* a, int lda, int M, int N, const float* rowscale, float* out, int accumulate,
                ftg_stream_t stream);
 int ftg_scale_outer_mask(const float* rowscale, const float* v, const float* mask, int ldm, float* out,
@@ -73,11 +76,15 @@ int ftg_bn_relu_fwd(const float* a, int lda, int B, int H, const float* gamma, c
 int ftg_bn_relu_bwd(const float* dout, int lddo, const float* a, int lda, int B, int H, const float* save_mean,
                     const float* save_invstd, const float* gamma, const float* beta, float* da, int ldda,
                     float* dgamma, float* dbeta, ftg_stream_t stream);
+/* same, additionally writes d(fc bias)[h] = sum_m da[m,h] (bias of the Linear feeding the BN) */
+int ftg_bn_relu_bwd_bias(const float* dout, int lddo, const float* a, int lda, int B, int H,
+                         const float* save_mean, const float* save_invstd, const float* gamma, const float* beta,
+                         float* da, int ldda, float* dgamma, float* dbeta, float* dbias_fc, ftg_stream_t stream);
 
 /* ---- apply_activate (tanh / gumbel-softmax) fwd+bwd, cond_loss fwd+bwd --------------------
  * Replaces apply_activate (ctgan.py:67-82) and cond_loss (ctgan.py:174-194), SURVEY K4/K5. */
 int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n_spans, const int* span_start,
-                     const int* span_width, const int* span_kind, float* out, int ldo, float tau,
+                     const int* span_width, const int* span_kind, const int* col_span, float* out, int ldo, float tau,
                      const float* u, int ldu, const int64_t* rng_state, int rng_stream, const float* cond,
                      int ldc, int n_opt, int use_noise, ftg_stream_t stream);
 int ftg_activate_bwd(const float* dout, int lddo, const float* act, int lda, int B, int n_spans,
@@ -114,6 +121,18 @@ int ftg_sample_rows(const int* row_ptr, const int* row_ids, const int* soft_csta
 int ftg_expand_rows(const float* vals, int n_tanh, const int* codes, int n_col, const int* rid,
                     const int* tanh_start, const int* soft_start, float* out, int ld, int dd, int B,
                     ftg_stream_t stream);
+
+/* fused batch preparation: (col,opt) draw + batch permutation + matching-row draw in one CTA,
+ * then one CTA per row writes z, c1, m1 (mode 0, G step) or z, c1 and the expanded real row
+ * with its permuted cond vector (mode 1, D step). */
+int ftg_prep_select(const float* cum_p, int n_col, int max_w, const int* soft_width, const int* soft_cstart,
+                    const int* row_ptr, const int* row_ids, int* col, int* opt, int* perm, int* rid, int B,
+                    const int64_t* rng_state, int s_col, int s_perm, int s_row, ftg_stream_t stream);
+int ftg_prep_rows(int mode, int* col, int* opt, const int* perm, const int* rid, const int* soft_cstart,
+                  float* z_out, int ldz, int E, float* c_out, int ldc, int n_opt, float* m_out, int ldm, int n_col,
+                  const float* vals, int n_tanh, const int* codes, const int* tanh_start, const int* soft_start,
+                  float* real_out, int ldr, int dd, const float* cum_p, int max_w, const int* soft_width, int B,
+                  const int64_t* rng_state, int s_z, int s_col, ftg_stream_t stream);
 
 /* ---- VGM codec (BGM_CTGAN_Transformer.transform / inverse_transform,
  *      S/dtds/features/transformers.py:385-464), K12/K13 ---------------------------------- */

@@ -42,7 +42,7 @@ def test_iteration_native_vs_reference(precision, tol):
         assert err <= tol * (1e-3 + gb.abs().max().item()), (name, "grad", err, gb.abs().max().item())
         # Adam normalises the update to ~lr, so parameters agree to a few lr in the worst case
         perr = (a.data - b.data).abs().max().item()
-        assert perr <= (5e-6 if precision == "fp32" else 1.5e-3), (name, "param", perr)
+        assert perr <= (2e-4 if precision == "fp32" else 1.5e-3), (name, "param", perr)
 
 
 def test_graph_replay_trains():
