@@ -79,6 +79,13 @@ __device__ __forceinline__ float block_sum(float v, float* smem32) {
 // ------------------------------------------------------------- GEMM epilogue
 #include "../include/fedtgan_b200.h"
 
+// Dropout uniform of element (m, n): Philox block (m, n/4), component n%4 -- so that a thread
+// owning 4 consecutive columns needs one Philox evaluation.
+__device__ __forceinline__ Philox4 ftg_dropout_block(const ftg_gemm_args& p, int m, int n4) {
+  return philox4x32_10((uint64_t)p.rng_state[0], (uint64_t)p.rng_state[1], (uint32_t)p.rng_stream,
+                       (uint32_t)(m * ((p.N + 3) >> 2) + n4));
+}
+
 // Applies the fused epilogue to accumulator value `acc` of element (m, n) and stores it.
 __device__ __forceinline__ void ftg_epilogue_store(const ftg_gemm_args& p, int m, int n, float acc) {
   float v = p.alpha * acc;
@@ -86,8 +93,14 @@ __device__ __forceinline__ void ftg_epilogue_store(const ftg_gemm_args& p, int m
   if (p.act) {
     float mult = v > 0.f ? 1.f : p.slope;
     if (p.act == 2) {
-      float u = p.drop_u ? p.drop_u[(size_t)m * p.ld_drop_u + n]
-                         : philox_uniform(p.rng_state, p.rng_stream, (uint32_t)(m * p.N + n));
+      float u;
+      if (p.drop_u) {
+        u = p.drop_u[(size_t)m * p.ld_drop_u + n];
+      } else {
+        Philox4 r = ftg_dropout_block(p, m, n >> 2);
+        uint32_t w = (n & 3) == 0 ? r.x : (n & 3) == 1 ? r.y : (n & 3) == 2 ? r.z : r.w;
+        u = u01(w);
+      }
       mult = (u >= p.drop_p) ? mult / (1.f - p.drop_p) : 0.f;
     }
     if (p.mask_out) p.mask_out[(size_t)m * p.ld_mask_out + n] = mult;

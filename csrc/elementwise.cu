@@ -184,14 +184,24 @@ extern "C" int ftg_expand_rows(const float* vals, int n_tanh, const int* codes, 
 __global__ void __launch_bounds__(1024) k_rowdot(const float* __restrict__ a, int lda, int M, int K,
                                                  const float* __restrict__ w, const float* bias, float* out,
                                                  const float* __restrict__ rowscale, float* loss_out) {
+  // 8 lanes per row (128 rows in flight per CTA), strided 8 apart so each lane keeps
+  // several independent loads in flight
   __shared__ float red[32];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int sub = threadIdx.x & 7, rloc = threadIdx.x >> 3, rows_per_pass = blockDim.x >> 3;
   float contrib = 0.f;
-  for (int row = blockIdx.x * nw + wid; row < M; row += gridDim.x * nw) {
+  for (int row0 = blockIdx.x * rows_per_pass; row0 < M; row0 += gridDim.x * rows_per_pass) {
+    const int row = row0 + rloc;
     float s = 0.f;
-    for (int k = lane; k < K; k += 32) s += a[(size_t)row * lda + k] * __ldg(w + k);
-    s = warp_sum(s) + (bias ? bias[0] : 0.f);
-    if (lane == 0) {
+    if (row < M) {
+      const float* ar = a + (size_t)row * lda;
+#pragma unroll 4
+      for (int k = sub; k < K; k += 8) s += ar[k] * __ldg(w + k);
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (row < M && sub == 0) {
+      s += bias ? bias[0] : 0.f;
       out[row] = s;
       if (rowscale) contrib += rowscale[row] * s;
     }
@@ -204,7 +214,7 @@ __global__ void __launch_bounds__(1024) k_rowdot(const float* __restrict__ a, in
 
 extern "C" int ftg_rowdot(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
                           ftg_stream_t stream) {
-  k_rowdot<<<ftg_cdiv(M, 32), 1024, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, out, nullptr, nullptr);
+  k_rowdot<<<ftg_cdiv(M, 128), 1024, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, out, nullptr, nullptr);
   FTG_LAUNCH_CHECK();
   return 0;
 }

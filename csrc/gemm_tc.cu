@@ -96,10 +96,88 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_b
   return d;
 }
 
+constexpr int SLD = BN + 4;                      // staged tile row stride (floats): 16 B aligned, conflict-free
+constexpr int CHUNKS = (BM * BN / 4) / 128;      // float4 chunks per epilogue thread (16)
+constexpr int EPI_BATCH = CHUNKS / 2;
+
+// Ragged / unaligned chunk: element-wise path (kept out of line: it is cold).
+__device__ __noinline__ void epilogue_scalar4(const ftg_gemm_args& p, int m, int n, float4 a) {
+#pragma unroll 1
+  for (int e = 0; e < 4; ++e) {
+    const float v = e == 0 ? a.x : e == 1 ? a.y : e == 2 ? a.z : a.w;
+    if (n + e < p.N) ftg_epilogue_store(p, m, n + e, v);
+  }
+}
+
+// Epilogue math on one float4 chunk (out of line: keeps the kernel small enough for the
+// instruction cache; the call overhead is irrelevant next to the global-memory latency).
+__device__ __noinline__ float4 epilogue_math4(const ftg_gemm_args& p, int m, int n, float4 a, float4 mk, float4 old,
+                                              float4 uu) {
+  float v0 = p.alpha * a.x, v1 = p.alpha * a.y, v2 = p.alpha * a.z, v3 = p.alpha * a.w;
+  if (p.bias) {
+    const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+    v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+  }
+  if (p.act) {
+    float m0 = v0 > 0.f ? 1.f : p.slope, m1 = v1 > 0.f ? 1.f : p.slope, m2 = v2 > 0.f ? 1.f : p.slope,
+          m3 = v3 > 0.f ? 1.f : p.slope;
+    if (p.act == 2) {
+      if (!p.drop_u) {
+        const Philox4 r = ftg_dropout_block(p, m, n >> 2);
+        uu = make_float4(u01(r.x), u01(r.y), u01(r.z), u01(r.w));
+      }
+      const float keep = 1.f / (1.f - p.drop_p);
+      m0 = (uu.x >= p.drop_p) ? m0 * keep : 0.f;
+      m1 = (uu.y >= p.drop_p) ? m1 * keep : 0.f;
+      m2 = (uu.z >= p.drop_p) ? m2 * keep : 0.f;
+      m3 = (uu.w >= p.drop_p) ? m3 * keep : 0.f;
+    }
+    if (p.mask_out) *reinterpret_cast<float4*>(p.mask_out + (size_t)m * p.ld_mask_out + n) = make_float4(m0, m1, m2, m3);
+    v0 *= m0; v1 *= m1; v2 *= m2; v3 *= m3;
+  }
+  if (p.mask_in) { v0 *= mk.x; v1 *= mk.y; v2 *= mk.z; v3 *= mk.w; }
+  if (p.accumulate) { v0 += old.x; v1 += old.y; v2 += old.z; v3 += old.w; }
+  return make_float4(v0, v1, v2, v3);
+}
+
+// Fused epilogue on EPI_BATCH float4 chunks per thread: all global loads first, then math,
+// then stores (the compiler cannot hoist loads over the stores itself: no-alias is unknown).
+__device__ __noinline__ void epilogue_batch(const ftg_gemm_args& p, bool vec_ok, const float* stage, int et,
+                                            int it0, int m0, int n0) {
+  float4 acc[EPI_BATCH], mk[EPI_BATCH], old[EPI_BATCH], uu[EPI_BATCH];
+  const bool need_u = (p.act == 2) && p.drop_u;
+#pragma unroll
+  for (int b = 0; b < EPI_BATCH; ++b) {
+    const int f = (it0 + b) * 128 + et, row = f >> 4, c4 = f & 15;
+    const int m = m0 + row, n = n0 + c4 * 4;
+    const bool full = vec_ok && m < p.M && (n + 3 < p.N);
+    acc[b] = *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4);
+    mk[b] = old[b] = uu[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (full) {
+      if (p.mask_in) mk[b] = *reinterpret_cast<const float4*>(p.mask_in + (size_t)m * p.ld_mask_in + n);
+      if (p.accumulate) old[b] = *reinterpret_cast<const float4*>(p.d + (size_t)m * p.ldd + n);
+      if (need_u) uu[b] = *reinterpret_cast<const float4*>(p.drop_u + (size_t)m * p.ld_drop_u + n);
+    }
+  }
+#pragma unroll
+  for (int b = 0; b < EPI_BATCH; ++b) {
+    const int f = (it0 + b) * 128 + et, row = f >> 4, c4 = f & 15;
+    const int m = m0 + row, n = n0 + c4 * 4;
+    if (m < p.M && n < p.N) {
+      if (vec_ok && (n + 3 < p.N))
+        *reinterpret_cast<float4*>(p.d + (size_t)m * p.ldd + n) = epilogue_math4(p, m, n, acc[b], mk[b], old[b], uu[b]);
+      else
+        epilogue_scalar4(p, m, n, acc[b]);
+    }
+  }
+}
+
 template <bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-          const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters) {
+          const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters,
+          int vec_ok_i) {
+  const bool vec_ok = vec_ok_i != 0;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;            // SWIZZLE_128B tiles need 1024 B alignment
@@ -192,30 +270,29 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     tmem_ld32(taddr + 32, r + 32);
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
     // Stage the accumulator tile through shared memory (the operand ring is idle once the
-    // last MMA has retired) so that global traffic is row-contiguous and the epilogue is a
-    // compact loop instead of 64 unrolled copies of the fused epilogue (I-cache!).
-    constexpr int SLD = BN + 1;
+    // last MMA has retired): afterwards thread `et` owns float4 chunks f = it*128 + et of the
+    // row-major tile, so all global traffic is 16 B per lane and fully coalesced, and the
+    // epilogue's loads (masks, uniforms, accumulate) are batched 8 deep for latency hiding.
     float* stage = reinterpret_cast<float*>(gen_base);
     {
-      float* myrow = stage + row_in_tile * SLD;
+      float4* myrow = reinterpret_cast<float4*>(stage + row_in_tile * SLD);
 #pragma unroll
-      for (int j = 0; j < BN; ++j) myrow[j] = __uint_as_float(r[j]);
+      for (int j = 0; j < BN / 4; ++j)
+        myrow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                               __uint_as_float(r[4 * j + 3]));
     }
-    __syncwarp();
-    const int rows_here = min(32, p.M - (m0 + q * 32));      // rows of this warp's quadrant inside M
+    const int et = threadIdx.x - 64;                           // 0..127 among the epilogue threads
+    asm volatile("bar.sync 1, 128;" ::: "memory");             // whole tile staged
     bool do_epilogue = true;
     if (split_k > 1) {
       // ---- split-K: publish the partial tile, last-arriving CTA reduces all partials
       const int tile = blockIdx.y * gridDim.x + blockIdx.x;
       const int n_tiles = gridDim.x * gridDim.y;
-      const int et = threadIdx.x - 64;                         // 0..127 among the epilogue threads
-      asm volatile("bar.sync 1, 128;" ::: "memory");           // whole tile staged
       float4* ws4 = reinterpret_cast<float4*>(workspace + ((size_t)z * n_tiles + tile) * (BM * BN));
 #pragma unroll
-      for (int it = 0; it < (BM * BN / 4) / 128; ++it) {       // 16 coalesced float4 per thread
-        const int f = it * 128 + et, row = f / (BN / 4), c4 = f % (BN / 4);
-        const float* sp = stage + row * SLD + c4 * 4;
-        ws4[f] = make_float4(sp[0], sp[1], sp[2], sp[3]);
+      for (int it = 0; it < CHUNKS; ++it) {
+        const int f = it * 128 + et;
+        ws4[f] = *reinterpret_cast<const float4*>(stage + (f >> 4) * SLD + (f & 15) * 4);
       }
       __threadfence();
       asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -230,35 +307,26 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         __threadfence();
         const size_t zstride4 = (size_t)n_tiles * (BM * BN / 4);
         const float4* wst4 = reinterpret_cast<const float4*>(workspace + (size_t)tile * (BM * BN));
-        float4 acc[16];
+        float4 acc[CHUNKS];
 #pragma unroll
-        for (int it = 0; it < 16; ++it) acc[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int it = 0; it < CHUNKS; ++it) acc[it] = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int zz = 0; zz < split_k; ++zz) {                 // fixed order => deterministic
 #pragma unroll
-          for (int it = 0; it < 16; ++it) {                    // 16 independent 16 B loads in flight
+          for (int it = 0; it < CHUNKS; ++it) {                // 16 independent 16 B loads in flight
             const float4 v = __ldcg(wst4 + zz * zstride4 + it * 128 + et);
             acc[it].x += v.x; acc[it].y += v.y; acc[it].z += v.z; acc[it].w += v.w;
           }
         }
 #pragma unroll
-        for (int it = 0; it < 16; ++it) {
-          const int f = it * 128 + et, row = f / (BN / 4), c4 = f % (BN / 4);
-          float* sp = stage + row * SLD + c4 * 4;
-          sp[0] = acc[it].x; sp[1] = acc[it].y; sp[2] = acc[it].z; sp[3] = acc[it].w;
+        for (int it = 0; it < CHUNKS; ++it) {
+          const int f = it * 128 + et;
+          *reinterpret_cast<float4*>(stage + (f >> 4) * SLD + (f & 15) * 4) = acc[it];   // own chunks only
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
       }
     }
     if (do_epilogue) {
-      for (int rr = 0; rr < rows_here; ++rr) {
-        const float* srow = stage + (q * 32 + rr) * SLD;
-        const int mm = m0 + q * 32 + rr;
-#pragma unroll
-        for (int half = 0; half < BN / 32; ++half) {
-          const int n = n0 + lane + 32 * half;
-          if (n < p.N) ftg_epilogue_store(p, mm, n, srow[lane + 32 * half]);
-        }
-      }
+      epilogue_batch(p, vec_ok, stage, et, 0, m0, n0);
+      epilogue_batch(p, vec_ok, stage, et, EPI_BATCH, m0, n0);
     }
     (void)m;
   }
@@ -308,6 +376,9 @@ bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, 
 template <bool A_MN, bool B_MN>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
            cudaStream_t stream) {
+  auto al = [](const void* ptr, int ld) { return ptr == nullptr || (((reinterpret_cast<uintptr_t>(ptr) & 15) == 0) && (ld & 3) == 0); };
+  const int vec_ok = al(p.d, p.ldd) && al(p.mask_in, p.ld_mask_in) && al(p.mask_out, p.ld_mask_out) &&
+                     al(p.drop_u, p.ld_drop_u) && al(p.bias, 0);
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
@@ -315,7 +386,7 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p,
     attr_done = true;
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
-  k_gemm_tc<A_MN, B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr);
+  k_gemm_tc<A_MN, B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr, vec_ok);
   ++g_ftg_launch_count;
   return (int)cudaPeekAtLastError();
 }

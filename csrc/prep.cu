@@ -51,21 +51,18 @@ k_prep_select(const float* __restrict__ cum_p, int n_col, int max_w, const int* 
     idx[i] = i;
   }
   __syncthreads();
-  for (int k = 2; k <= P2; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < P2; i += blockDim.x) {
-        int l = i ^ j;
-        if (l > i) {
-          bool up = ((i & k) == 0);
-          float a = key[i], b = key[l];
-          int ia = idx[i], ib = idx[l];
-          bool gt = (a > b) || (a == b && ia > ib);
-          if (gt == up) { key[i] = b; key[l] = a; idx[i] = ib; idx[l] = ia; }
-        }
-      }
-      __syncthreads();
+  // random permutation = argsort of the iid keys, by rank counting: rank(i) = #{j : key_j < key_i}
+  // (B^2 shared-memory broadcast reads, no barriers -- much cheaper than a bitonic network here)
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    const float ki = key[i];
+    int rank = 0;
+    for (int j = 0; j < B; ++j) {
+      const float kj = key[j];
+      rank += (kj < ki) || (kj == ki && j < i);
     }
+    idx[rank] = i;
   }
+  __syncthreads();
   for (int i = threadIdx.x; i < B; i += blockDim.x) {
     int src = idx[i];
     perm[i] = src;
