@@ -1,0 +1,149 @@
+"""``bench.py --impl reference``: time the unmodified reference on the same table / split.
+
+Topology is the reference's own: one federator process (rank 0 of the RPC world, CPU) plus
+one client process per GPU (``cuda:0`` of its own ``CUDA_VISIBLE_DEVICES``), all driven by
+the reference's ``run()``.  Under ``torchrun`` every rank starts its own client; rank 0 also
+starts the federator.  The per-round time is the reference's own measurement
+(``timestamp_experiment.csv``, ``Server/dtds/distributed.py:795-829``: wall clock of the whole
+round incl. sampling 40 000 rows and writing the CSV); the first ``warmup`` rounds are
+dropped.  Files the reference expects but does not create are prepared here
+(``models/``, ``Intrusion_result/``, ``models/Intrusion_train.npz`` built with the
+reference's own ``FileGenerator``).
+"""
+from __future__ import annotations
+
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = os.path.join(HERE, "_ref")
+PUBLISHED_EPOCHS_PER_S = 1.0 / 24.2
+
+
+def _prepare_dirs(base, schema, df, shards):
+    import numpy as np
+
+    os.makedirs(os.path.join(base, "server", "models"), exist_ok=True)
+    os.makedirs(os.path.join(base, "server", "Intrusion_result"), exist_ok=True)
+    for i, sh in enumerate(shards):
+        d = os.path.join(base, f"client{i + 1}", "data", "raw")
+        os.makedirs(d, exist_ok=True)
+        sh.to_csv(os.path.join(d, "Intrusion_train.csv"), index=False)
+    # models/Intrusion_train.npz = the full table label-encoded exactly as the reference's
+    # FileGenerator would (sorted-string LabelEncoder ids, log(x+1) on non-negative columns)
+    code = f"""
+import sys, pickle, json
+sys.path.insert(0, {REF!r}); sys.path.insert(0, {HERE!r})
+import ref_worker; ref_worker.apply_shims()
+import numpy as np, pandas as pd
+from sklearn import preprocessing
+from dtds.data.utils.file_generator import FileGenerator
+df = pd.read_csv({os.path.join(base, 'full.csv')!r})
+cols, cats, nonneg = json.loads({json.dumps(json.dumps([schema.columns, schema.categorical, schema.nonnegative]))})
+fg = FileGenerator(dataframe=df[cols], file_name='Intrusion_train', problem_type='', target_col={schema.target!r},
+                   categorical_list=list(cats), non_negative_columns=list(nonneg), date_columns={{}})
+les = []
+for c in fg.df.columns:
+    if c in cats:
+        les.append(preprocessing.LabelEncoder().fit(fg.df[c].astype(str)))
+fg.generate_data(fg.generate_meta_data(), les, 'prep')
+import glob, shutil
+shutil.copy(glob.glob('dtds/saved_models/*prep/*.npz')[0], {os.path.join(base, 'server', 'models', 'Intrusion_train.npz')!r})
+"""
+    df.to_csv(os.path.join(base, "full.csv"), index=False)
+    prep_dir = os.path.join(base, "prep")
+    os.makedirs(prep_dir, exist_ok=True)
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", PYTHONPATH="")
+    subprocess.run([sys.executable, "-c", code], cwd=prep_dir, env=env, check=True,
+                   stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+
+
+def _spawn(spec, gpu, log):
+    env = dict(os.environ)
+    env["CUDA_VISIBLE_DEVICES"] = "" if gpu is None else str(gpu)
+    env["PYTHONPATH"] = ""
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "GROUP_RANK", "LOCAL_WORLD_SIZE",
+              "TORCHELASTIC_RUN_ID"):
+        env.pop(k, None)
+    fh = open(log, "w")
+    return subprocess.Popen([sys.executable, os.path.join(HERE, "ref_worker.py"), json.dumps(spec)],
+                            env=env, stdout=fh, stderr=subprocess.STDOUT)
+
+
+def run_reference_bench(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if not os.path.isdir(os.path.join(REF, "dtds")):
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is not installed (see DESIGN.md)"}))
+        return
+    sys.path.insert(0, ROOT)
+    from fed_tgan_b200.data.schemas import get_schema, make_table, split_table   # data generation only
+
+    schema = get_schema(args.config, rows=args.rows)
+    n_clients = max(world, 1)
+    epochs = max(args.warmup, 1) + args.steps
+    base_port = 23000 + (os.getpid() % 2000 if world == 1 else int(os.environ.get("MASTER_PORT", "29500")) % 2000)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        box = [tempfile.mkdtemp(prefix="fedtgan_ref_") if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        base = box[0]
+    else:
+        base = tempfile.mkdtemp(prefix="fedtgan_ref_")
+    if rank == 0:
+        df = make_table(schema, seed=0)
+        shards = split_table(df, n_clients, "skewed" if args.config == "covertype" else "iid", seed=0)
+        _prepare_dirs(base, schema, df, shards)
+    if world > 1:
+        dist.barrier()
+    common = dict(world_size=n_clients + 1, port=base_port, columns=schema.columns, categorical=schema.categorical,
+                  nonnegative=schema.nonnegative, target=schema.target, epochs=epochs)
+    procs = []
+    t0 = time.time()
+    if rank == 0:
+        procs.append(_spawn(dict(common, rank=0, cwd=os.path.join(base, "server")), None,
+                            os.path.join(base, "server.log")))
+    procs.append(_spawn(dict(common, rank=rank + 1, cwd=os.path.join(base, f"client{rank + 1}")), local,
+                        os.path.join(base, f"client{rank + 1}.log")))
+    rc = [p.wait() for p in procs]
+    wall = time.time() - t0
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        out = {"impl": "reference", "metric": "federated_epochs_per_sec", "unit": "federated_epochs/s",
+               "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1), "higher_is_better": True,
+               "scaling": "strong", "dtype": "fp32", "data": "synthetic"}
+        ts_path = os.path.join(base, "server", "timestamp_experiment.csv")
+        if any(rc) or not os.path.exists(ts_path):
+            tail = ""
+            try:
+                tail = open(os.path.join(base, "server.log")).read()[-400:].replace("\n", " | ")
+            except Exception:
+                pass
+            out["unavailable"] = f"reference run failed rc={rc}: {tail}"
+        else:
+            times = [float(x) for x in open(ts_path).read().split()]
+            timed = times[-args.steps:]
+            sec = sum(timed)
+            out.update({
+                "value": args.steps / sec, "ms_per_step": 1e3 * sec / args.steps, "vs_baseline": (args.steps / sec) / PUBLISHED_EPOCHS_PER_S,
+                "e2e": {"value": args.steps / sec, "unit": "federated_epochs/s",
+                        "note": "the reference's round is end to end by construction (numpy sampling + H2D every step, D2H + CPU sampling + CSV every round)"},
+                "timing": "reference's own per-round wall clock (timestamp_experiment.csv), warm-up rounds dropped",
+                "total_wall_s": round(wall, 1), "per_round_s": [round(t, 3) for t in times],
+                "config": {"table": f"{schema.name}-shape synthetic {schema.rows}x{len(schema.columns)}", "clients": n_clients,
+                           "split": "iid", "batch_per_client": 500, "sample_rows_per_round": 40000,
+                           "code": "baseline/_ref/dtds (unmodified Server/dtds), torch RPC TensorPipe, CPU aggregation"},
+            })
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
