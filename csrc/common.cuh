@@ -5,6 +5,7 @@
 #include <math.h>
 
 #define FTG_ERR_UNSUPPORTED 1000
+#define FTG_ERR_SCRATCH_TOO_SMALL 1001
 
 extern int g_ftg_launch_count;   // defined in elementwise.cu
 

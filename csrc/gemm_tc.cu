@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include <cuda.h>
 #include <mutex>
+#include <cstdio>
 
 namespace {
 
@@ -432,4 +433,98 @@ extern "C" int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* worksp
                           : launch<true, false>(ma, mb, p, split_k, workspace, tile_counters, s);
   return p.b_t ? launch<false, true>(ma, mb, p, split_k, workspace, tile_counters, s)
                : launch<false, false>(ma, mb, p, split_k, workspace, tile_counters, s);
+}
+
+// ---------------------------------------------------------------------------------------
+// ftg_gemm_tc_noalloc: the same GEMM for callers that must not allocate device memory.
+//
+// Some users of this library cannot call cudaMalloc at the point where they need a GEMM:
+// a plugin running inside a host application that has handed the whole device heap to its
+// own pool, a fail-safe path that has to keep working when the device is out of memory, a
+// latency-critical loop that cannot afford cudaMalloc's implicit device synchronisation.
+// ftg_gemm_tc() asks such a caller for a split-K workspace and tile counters; this variant
+// takes them from a fixed, file-scope device array instead.  The caller still passes the
+// operands and the output.
+//
+//  * The array costs FTG_NOALLOC_SCRATCH_BYTES (8 MiB + 4 KiB) of device memory on every
+//    GPU that loads the library, from load until process exit.
+//  * Requests that need more (split_k * tiles * 32 KiB of partial tiles, or more than
+//    FTG_NOALLOC_MAX_TILES output tiles) are refused with FTG_ERR_SCRATCH_TOO_SMALL and a
+//    message in ftg_last_error_message(); lower split_k (split_k = 1 needs no scratch).
+//  * The first call on a device resolves the array's device address (cudaGetSymbolAddress,
+//    once per device, with that device current).  Make that first call before any stream
+//    capture begins on the device.
+//  * Every call on a device shares the one array: the tile counters are cleared at the start
+//    of each call and the partial tiles are fully rewritten before they are read, but two
+//    calls whose kernels overlap on the GPU (different streams) race on it.  Serialise them.
+//  * No cudaMalloc, cudaFree or allocating library routine is called on this path.
+// ---------------------------------------------------------------------------------------
+namespace {
+
+constexpr long long NOALLOC_WS_BYTES = 8ll << 20;
+constexpr int NOALLOC_MAX_TILES = 1024;
+constexpr long long NOALLOC_COUNTER_BYTES = (long long)NOALLOC_MAX_TILES * sizeof(int);
+
+// [ tile counters (4 KiB) | split-K partial tiles (8 MiB) ]
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_COUNTER_BYTES + NOALLOC_WS_BYTES];
+
+constexpr int MAX_DEVICES = 64;
+unsigned char* g_noalloc_ptr[MAX_DEVICES] = {nullptr};
+std::mutex g_noalloc_mutex;
+thread_local char g_last_error[256] = "";
+
+// `g_noalloc_scratch` named in host code is only a host-side stand-in for the symbol; the
+// address a kernel can use has to be asked for, per device.
+int noalloc_device_ptr(unsigned char** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= MAX_DEVICES) return FTG_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[dev]) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess) {
+      snprintf(g_last_error, sizeof(g_last_error), "ftg_gemm_tc_noalloc: cudaGetSymbolAddress failed on device %d: %s",
+               dev, cudaGetErrorString(e));
+      return (int)e;
+    }
+    g_noalloc_ptr[dev] = static_cast<unsigned char*>(ptr);
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" const char* ftg_last_error_message(void) { return g_last_error; }
+
+extern "C" long long ftg_gemm_tc_noalloc_max_workspace_bytes(void) { return NOALLOC_WS_BYTES; }
+
+extern "C" int ftg_gemm_tc_noalloc(const ftg_gemm_args* args, int split_k, ftg_stream_t stream) {
+  g_last_error[0] = 0;
+  if (!args) return FTG_ERR_UNSUPPORTED;
+  if (split_k < 1) split_k = 1;
+  const int nkb = ftg_cdiv(args->K > 0 ? args->K : 1, BK);
+  if (split_k > nkb) split_k = nkb;
+  const int tiles = ftg_gemm_tc_num_tiles(args->M, args->N);
+  const long long need = ftg_gemm_tc_workspace_bytes(args->M, args->N, split_k);
+  if (split_k > 1 && (need > NOALLOC_WS_BYTES || tiles > NOALLOC_MAX_TILES)) {
+    snprintf(g_last_error, sizeof(g_last_error),
+             "ftg_gemm_tc_noalloc: M=%d N=%d split_k=%d needs %lld bytes of split-K scratch in %d tiles; the built-in "
+             "scratch holds %lld bytes and %d tiles (use a smaller split_k, or ftg_gemm_tc with your own workspace)",
+             args->M, args->N, split_k, need, tiles, NOALLOC_WS_BYTES, NOALLOC_MAX_TILES);
+    return FTG_ERR_SCRATCH_TOO_SMALL;
+  }
+  unsigned char* base = nullptr;
+  int rc = noalloc_device_ptr(&base);
+  if (rc) return rc;
+  int* counters = reinterpret_cast<int*>(base);
+  float* workspace = reinterpret_cast<float*>(base + NOALLOC_COUNTER_BYTES);
+  if (split_k > 1) {
+    // the counters must start at zero; an earlier call that died half-way could have left them dirty
+    cudaError_t e = cudaMemsetAsync(counters, 0, (size_t)tiles * sizeof(int), (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+  }
+  return ftg_gemm_tc(args, split_k, workspace, counters, stream);
 }

@@ -52,6 +52,20 @@ int ftg_gemm_simt(const ftg_gemm_args* args, ftg_stream_t stream);
  * Returns 1000 (FTG_ERR_UNSUPPORTED) when the shape/alignment cannot be handled.        */
 int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* workspace, int* tile_counters,
                 ftg_stream_t stream);
+/* (No counterpart in the reference.)  ftg_gemm_tc for callers that cannot allocate device
+ * memory -- e.g. a plugin inside a host that owns the whole device heap, an out-of-memory
+ * fail-safe path, a loop that cannot take cudaMalloc's device synchronisation.  The split-K
+ * workspace and tile counters come from a fixed device array built into the library
+ * (8 MiB + 4 KiB per GPU, held from library load to process exit); operands and output are
+ * still the caller's.  Returns 1001 (FTG_ERR_SCRATCH_TOO_SMALL, text in
+ * ftg_last_error_message()) when split_k * tiles * 32 KiB exceeds
+ * ftg_gemm_tc_noalloc_max_workspace_bytes() or the output has more than 1024 tiles.  The
+ * first call on a device looks the array up (make it before any stream capture on that
+ * device).  All calls on a device share the array: do not let two of them overlap on the
+ * GPU.  Calls no cudaMalloc / cudaFree / allocating routine.                              */
+int ftg_gemm_tc_noalloc(const ftg_gemm_args* args, int split_k, ftg_stream_t stream);
+long long ftg_gemm_tc_noalloc_max_workspace_bytes(void);
+const char* ftg_last_error_message(void);
 int ftg_gemm_tc_choose_split(int M, int N, int K);
 long long ftg_gemm_tc_workspace_bytes(int M, int N, int split_k);
 int ftg_gemm_tc_num_tiles(int M, int N);
