@@ -101,8 +101,12 @@ constexpr int SLD = BN + 4;                      // staged tile row stride (floa
 constexpr int CHUNKS = (BM * BN / 4) / 128;      // float4 chunks per epilogue thread (16)
 constexpr int EPI_BATCH = CHUNKS / 2;
 
-// Ragged / unaligned chunk: element-wise path (kept out of line: it is cold).
-__device__ __noinline__ void epilogue_scalar4(const ftg_gemm_args& p, int m, int n, float4 a) {
+// Epilogue specialisations (compile-time, so the unrolled code stays tiny and branch-free).
+enum { EPI_PLAIN = 0, EPI_ACC = 1, EPI_BIAS = 2, EPI_BIAS_ACT = 3, EPI_MASK = 4, EPI_GENERIC = 5 };
+
+// Ragged / unaligned chunk (and the generic flag combination): element-wise path, out of line
+// because it is cold; `p` by value so that the kernel itself never spills its parameters.
+__device__ __noinline__ void epilogue_scalar4(const ftg_gemm_args p, int m, int n, float4 a) {
 #pragma unroll 1
   for (int e = 0; e < 4; ++e) {
     const float v = e == 0 ? a.x : e == 1 ? a.y : e == 2 ? a.z : a.w;
@@ -110,70 +114,73 @@ __device__ __noinline__ void epilogue_scalar4(const ftg_gemm_args& p, int m, int
   }
 }
 
-// Epilogue math on one float4 chunk (out of line: keeps the kernel small enough for the
-// instruction cache; the call overhead is irrelevant next to the global-memory latency).
-__device__ __noinline__ float4 epilogue_math4(const ftg_gemm_args& p, int m, int n, float4 a, float4 mk, float4 old,
-                                              float4 uu) {
-  float v0 = p.alpha * a.x, v1 = p.alpha * a.y, v2 = p.alpha * a.z, v3 = p.alpha * a.w;
-  if (p.bias) {
-    const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n));
-    v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
-  }
-  if (p.act) {
-    float m0 = v0 > 0.f ? 1.f : p.slope, m1 = v1 > 0.f ? 1.f : p.slope, m2 = v2 > 0.f ? 1.f : p.slope,
-          m3 = v3 > 0.f ? 1.f : p.slope;
-    if (p.act == 2) {
-      if (!p.drop_u) {
-        const Philox4 r = ftg_dropout_block(p, m, n >> 2);
-        uu = make_float4(u01(r.x), u01(r.y), u01(r.z), u01(r.w));
+// Fused epilogue: thread `et` owns float4 chunks f = it*128 + et of the staged 128 x 64 tile.
+// Two batches of 8 chunks: all global loads of a batch are issued before its math and stores
+// (the compiler cannot hoist loads over the stores itself: no-alias is unknown).
+template <int EPI>
+__device__ __forceinline__ void epilogue_tile(const ftg_gemm_args& p, bool vec_ok, const float* stage, int et, int m0,
+                                              int n0) {
+#pragma unroll 1
+  for (int batch = 0; batch < 2; ++batch) {
+    float4 acc[EPI_BATCH], aux[EPI_BATCH];
+#pragma unroll
+    for (int b = 0; b < EPI_BATCH; ++b) {
+      const int f = (batch * EPI_BATCH + b) * 128 + et, row = f >> 4, c4 = f & 15;
+      const int m = m0 + row, n = n0 + c4 * 4;
+      const bool full = vec_ok && m < p.M && (n + 3 < p.N);
+      acc[b] = *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4);
+      aux[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (full) {
+        if (EPI == EPI_ACC) aux[b] = *reinterpret_cast<const float4*>(p.d + (size_t)m * p.ldd + n);
+        if (EPI == EPI_MASK) aux[b] = *reinterpret_cast<const float4*>(p.mask_in + (size_t)m * p.ld_mask_in + n);
+        if (EPI == EPI_BIAS_ACT && p.drop_u) aux[b] = *reinterpret_cast<const float4*>(p.drop_u + (size_t)m * p.ld_drop_u + n);
       }
-      const float keep = 1.f / (1.f - p.drop_p);
-      m0 = (uu.x >= p.drop_p) ? m0 * keep : 0.f;
-      m1 = (uu.y >= p.drop_p) ? m1 * keep : 0.f;
-      m2 = (uu.z >= p.drop_p) ? m2 * keep : 0.f;
-      m3 = (uu.w >= p.drop_p) ? m3 * keep : 0.f;
     }
-    if (p.mask_out) *reinterpret_cast<float4*>(p.mask_out + (size_t)m * p.ld_mask_out + n) = make_float4(m0, m1, m2, m3);
-    v0 *= m0; v1 *= m1; v2 *= m2; v3 *= m3;
-  }
-  if (p.mask_in) { v0 *= mk.x; v1 *= mk.y; v2 *= mk.z; v3 *= mk.w; }
-  if (p.accumulate) { v0 += old.x; v1 += old.y; v2 += old.z; v3 += old.w; }
-  return make_float4(v0, v1, v2, v3);
-}
-
-// Fused epilogue on EPI_BATCH float4 chunks per thread: all global loads first, then math,
-// then stores (the compiler cannot hoist loads over the stores itself: no-alias is unknown).
-__device__ __noinline__ void epilogue_batch(const ftg_gemm_args& p, bool vec_ok, const float* stage, int et,
-                                            int it0, int m0, int n0) {
-  float4 acc[EPI_BATCH], mk[EPI_BATCH], old[EPI_BATCH], uu[EPI_BATCH];
-  const bool need_u = (p.act == 2) && p.drop_u;
 #pragma unroll
-  for (int b = 0; b < EPI_BATCH; ++b) {
-    const int f = (it0 + b) * 128 + et, row = f >> 4, c4 = f & 15;
-    const int m = m0 + row, n = n0 + c4 * 4;
-    const bool full = vec_ok && m < p.M && (n + 3 < p.N);
-    acc[b] = *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4);
-    mk[b] = old[b] = uu[b] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (full) {
-      if (p.mask_in) mk[b] = *reinterpret_cast<const float4*>(p.mask_in + (size_t)m * p.ld_mask_in + n);
-      if (p.accumulate) old[b] = *reinterpret_cast<const float4*>(p.d + (size_t)m * p.ldd + n);
-      if (need_u) uu[b] = *reinterpret_cast<const float4*>(p.drop_u + (size_t)m * p.ld_drop_u + n);
-    }
-  }
-#pragma unroll
-  for (int b = 0; b < EPI_BATCH; ++b) {
-    const int f = (it0 + b) * 128 + et, row = f >> 4, c4 = f & 15;
-    const int m = m0 + row, n = n0 + c4 * 4;
-    if (m < p.M && n < p.N) {
-      if (vec_ok && (n + 3 < p.N))
-        *reinterpret_cast<float4*>(p.d + (size_t)m * p.ldd + n) = epilogue_math4(p, m, n, acc[b], mk[b], old[b], uu[b]);
-      else
+    for (int b = 0; b < EPI_BATCH; ++b) {
+      const int f = (batch * EPI_BATCH + b) * 128 + et, row = f >> 4, c4 = f & 15;
+      const int m = m0 + row, n = n0 + c4 * 4;
+      if (m >= p.M || n >= p.N) continue;
+      if (EPI == EPI_GENERIC || !(vec_ok && (n + 3 < p.N))) {
         epilogue_scalar4(p, m, n, acc[b]);
+        continue;
+      }
+      float v0 = p.alpha * acc[b].x, v1 = p.alpha * acc[b].y, v2 = p.alpha * acc[b].z, v3 = p.alpha * acc[b].w;
+      if (EPI == EPI_BIAS || EPI == EPI_BIAS_ACT) {
+        const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+        v0 += bb.x; v1 += bb.y; v2 += bb.z; v3 += bb.w;
+      }
+      if (EPI == EPI_BIAS_ACT) {
+        float4 u = aux[b];
+        if (p.act == 2 && !p.drop_u) {
+          const Philox4 r = ftg_dropout_block(p, m, n >> 2);
+          u = make_float4(u01(r.x), u01(r.y), u01(r.z), u01(r.w));
+        }
+        float k0 = v0 > 0.f ? 1.f : p.slope, k1 = v1 > 0.f ? 1.f : p.slope, k2 = v2 > 0.f ? 1.f : p.slope,
+              k3 = v3 > 0.f ? 1.f : p.slope;
+        if (p.act == 2) {
+          const float keep = 1.f / (1.f - p.drop_p);
+          k0 = (u.x >= p.drop_p) ? k0 * keep : 0.f;
+          k1 = (u.y >= p.drop_p) ? k1 * keep : 0.f;
+          k2 = (u.z >= p.drop_p) ? k2 * keep : 0.f;
+          k3 = (u.w >= p.drop_p) ? k3 * keep : 0.f;
+        }
+        if (p.mask_out) *reinterpret_cast<float4*>(p.mask_out + (size_t)m * p.ld_mask_out + n) = make_float4(k0, k1, k2, k3);
+        v0 *= k0; v1 *= k1; v2 *= k2; v3 *= k3;
+      }
+      if (EPI == EPI_MASK) { v0 *= aux[b].x; v1 *= aux[b].y; v2 *= aux[b].z; v3 *= aux[b].w; }
+      if (EPI == EPI_ACC) { v0 += aux[b].x; v1 += aux[b].y; v2 += aux[b].z; v3 += aux[b].w; }
+      *reinterpret_cast<float4*>(p.d + (size_t)m * p.ldd + n) = make_float4(v0, v1, v2, v3);
     }
   }
 }
 
-template <bool A_MN, bool B_MN>
+// Optional in-kernel timeline of CTA (0,0,0) (clock64 at phase boundaries) for latency analysis.
+__device__ long long g_gemm_timeline[16];
+__device__ int g_gemm_timeline_on = 0;
+#define TL(i) do { if (g_gemm_timeline_on && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) g_gemm_timeline[i] = clock64(); } while (0)
+
+template <bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
           const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters,
@@ -196,6 +203,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   const int kb0 = (int)((long long)z * nkb / split_k), kb1 = (int)((long long)(z + 1) * nkb / split_k);
 
   if (threadIdx.x == 0) {
+    TL(0);
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -215,6 +223,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     int s = 0;
     uint32_t phase = 0;
+    TL(1);
     for (int kb = kb0; kb < kb1; ++kb) {
       mbar_wait(empty_bar(s), phase ^ 1u);
       const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
@@ -234,6 +243,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       }
       if (++s == STAGES) { s = 0; phase ^= 1u; }
     }
+    TL(2);
   } else if (warp == 1 && lane == 0) {
     // -------------------------------------------------------------- MMA issuer
     // instruction descriptor: D=f32, A=B=tf32, majors, N=64, M=128
@@ -243,6 +253,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     uint32_t phase = 0;
     for (int kb = kb0; kb < kb1; ++kb) {
       mbar_wait(full_bar(s), phase);
+      if (kb == kb0) TL(3);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
 #pragma unroll
@@ -258,12 +269,14 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       if (++s == STAGES) { s = 0; phase ^= 1u; }
     }
     umma_commit(tmem_full_bar);                 // accumulator complete
+    TL(4);
   } else if (warp >= 2) {
     // ---------------------------------------------------------------- epilogue
     const int q = warp & 3;                      // TMEM lane quadrant owned by this warp
     const int row_in_tile = q * 32 + lane;
     const int m = m0 + row_in_tile;
     mbar_wait(tmem_full_bar, 0);
+    if (threadIdx.x == 64) TL(5);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     uint32_t r[64];
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
@@ -284,6 +297,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     }
     const int et = threadIdx.x - 64;                           // 0..127 among the epilogue threads
     asm volatile("bar.sync 1, 128;" ::: "memory");             // whole tile staged
+    if (threadIdx.x == 64) TL(6);
     bool do_epilogue = true;
     if (split_k > 1) {
       // ---- split-K: publish the partial tile, last-arriving CTA reduces all partials
@@ -325,14 +339,16 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         }
       }
     }
+    if (threadIdx.x == 64) TL(7);
     if (do_epilogue) {
-      epilogue_batch(p, vec_ok, stage, et, 0, m0, n0);
-      epilogue_batch(p, vec_ok, stage, et, EPI_BATCH, m0, n0);
+      epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0);
     }
+    if (threadIdx.x == 64) TL(8);
     (void)m;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
+  if (threadIdx.x == 0) TL(9);
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
@@ -374,25 +390,54 @@ bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, 
   return r == CUDA_SUCCESS;
 }
 
+template <bool A_MN, bool B_MN, int EPI>
+int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
+               int vec_ok, cudaStream_t stream) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    attr_done = true;
+  }
+  dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
+  k_gemm_tc<A_MN, B_MN, EPI><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr, vec_ok);
+  ++g_ftg_launch_count;
+  return (int)cudaPeekAtLastError();
+}
+
 template <bool A_MN, bool B_MN>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
            cudaStream_t stream) {
   auto al = [](const void* ptr, int ld) { return ptr == nullptr || (((reinterpret_cast<uintptr_t>(ptr) & 15) == 0) && (ld & 3) == 0); };
   const int vec_ok = al(p.d, p.ldd) && al(p.mask_in, p.ld_mask_in) && al(p.mask_out, p.ld_mask_out) &&
                      al(p.drop_u, p.ld_drop_u) && al(p.bias, 0);
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    attr_done = true;
+  // pick the epilogue specialisation that matches the flag combination exactly
+  int epi = EPI_GENERIC;
+  const bool b = p.bias != nullptr, a = p.act != 0, mi = p.mask_in != nullptr, acc = p.accumulate != 0;
+  if (!b && !a && !mi && !acc) epi = EPI_PLAIN;
+  else if (!b && !a && !mi && acc) epi = EPI_ACC;
+  else if (b && !a && !mi && !acc) epi = EPI_BIAS;
+  else if (b && a && !mi && !acc) epi = EPI_BIAS_ACT;
+  else if (!b && !a && mi && !acc) epi = EPI_MASK;
+  switch (epi) {
+    case EPI_PLAIN: return launch_epi<A_MN, B_MN, EPI_PLAIN>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
+    case EPI_ACC: return launch_epi<A_MN, B_MN, EPI_ACC>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
+    case EPI_BIAS: return launch_epi<A_MN, B_MN, EPI_BIAS>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
+    case EPI_BIAS_ACT: return launch_epi<A_MN, B_MN, EPI_BIAS_ACT>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
+    case EPI_MASK: return launch_epi<A_MN, B_MN, EPI_MASK>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
+    default: return launch_epi<A_MN, B_MN, EPI_GENERIC>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
   }
-  dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
-  k_gemm_tc<A_MN, B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr, vec_ok);
-  ++g_ftg_launch_count;
-  return (int)cudaPeekAtLastError();
 }
 
 }  // namespace
+
+// debug: enable / read the in-kernel timeline of CTA (0,0,0)
+extern "C" int ftg_gemm_tc_timeline(int enable, long long* out16) {
+  cudaError_t e = cudaMemcpyToSymbol(g_gemm_timeline_on, &enable, sizeof(int));
+  if (e != cudaSuccess) return (int)e;
+  if (out16) e = cudaMemcpyFromSymbol(out16, g_gemm_timeline, 16 * sizeof(long long));
+  return (int)e;
+}
 
 extern "C" int ftg_gemm_tc_num_tiles(int M, int N) { return ftg_cdiv(M, BM) * ftg_cdiv(N, BN); }
 
