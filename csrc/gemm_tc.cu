@@ -9,7 +9,7 @@
 // * both operand majors are supported natively (K-major: [rows, K]; MN-major: [K, rows]),
 //   so forward (X.W^T), dgrad (dY.W) and wgrad (dY^T.X) need no transposed copies;
 // * warp roles: warp 0 lane 0 = TMA producer, warp 1 = TMEM allocator + lane 0 MMA issuer,
-//   warps 2..5 = epilogue (each owns one 32-lane TMEM quadrant); 4-stage mbarrier ring;
+//   warps 2..5 = epilogue (each owns one 32-lane TMEM quadrant); 6-stage mbarrier ring;
 // * split-K: grid.z CTAs write partial tiles to a caller-provided workspace; the CTA that
 //   arrives last at the tile's counter reduces them in fixed z order (deterministic) and
 //   applies the fused epilogue.  The CTGAN shapes are skinny (M = 50..500, K up to ~8000),
@@ -22,7 +22,7 @@
 namespace {
 
 constexpr int BM = 128, BN = 64, BK = 32;       // BK floats = 128 B = one swizzle row
-constexpr int STAGES = 4;
+constexpr int STAGES = 6;
 constexpr int A_STAGE_BYTES = BM * BK * 4;      // 16 KB
 constexpr int B_STAGE_BYTES = BN * BK * 4;      //  8 KB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -119,16 +119,18 @@ __device__ __noinline__ void epilogue_scalar4(const ftg_gemm_args p, int m, int 
 // (the compiler cannot hoist loads over the stores itself: no-alias is unknown).
 template <int EPI>
 __device__ __forceinline__ void epilogue_tile(const ftg_gemm_args& p, bool vec_ok, const float* stage, int et, int m0,
-                                              int n0) {
+                                              int n0, int f_base, int n_iter) {
+  // chunks f = f_base + it*128 + et, it < n_iter (whole tile: f_base 0, n_iter 16)
 #pragma unroll 1
-  for (int batch = 0; batch < 2; ++batch) {
+  for (int batch = 0; batch * EPI_BATCH < n_iter; ++batch) {
     float4 acc[EPI_BATCH], aux[EPI_BATCH];
 #pragma unroll
     for (int b = 0; b < EPI_BATCH; ++b) {
-      const int f = (batch * EPI_BATCH + b) * 128 + et, row = f >> 4, c4 = f & 15;
-      const int m = m0 + row, n = n0 + c4 * 4;
+      const int it = batch * EPI_BATCH + b;
+      const int f = f_base + it * 128 + et, row = f >> 4, c4 = f & 15;
+      const int m = (it < n_iter) ? m0 + row : p.M, n = n0 + c4 * 4;
       const bool full = vec_ok && m < p.M && (n + 3 < p.N);
-      acc[b] = *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4);
+      acc[b] = (it < n_iter) ? *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
       aux[b] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (full) {
         if (EPI == EPI_ACC) aux[b] = *reinterpret_cast<const float4*>(p.d + (size_t)m * p.ldd + n);
@@ -138,8 +140,9 @@ __device__ __forceinline__ void epilogue_tile(const ftg_gemm_args& p, bool vec_o
     }
 #pragma unroll
     for (int b = 0; b < EPI_BATCH; ++b) {
-      const int f = (batch * EPI_BATCH + b) * 128 + et, row = f >> 4, c4 = f & 15;
-      const int m = m0 + row, n = n0 + c4 * 4;
+      const int it = batch * EPI_BATCH + b;
+      const int f = f_base + it * 128 + et, row = f >> 4, c4 = f & 15;
+      const int m = (it < n_iter) ? m0 + row : p.M, n = n0 + c4 * 4;
       if (m >= p.M || n >= p.N) continue;
       if (EPI == EPI_GENERIC || !(vec_ok && (n + 3 < p.N))) {
         epilogue_scalar4(p, m, n, acc[b]);
@@ -184,7 +187,7 @@ template <bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
           const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters,
-          int vec_ok_i) {
+          int vec_ok_i, int cluster_mode) {
   const bool vec_ok = vec_ok_i != 0;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -298,8 +301,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     const int et = threadIdx.x - 64;                           // 0..127 among the epilogue threads
     asm volatile("bar.sync 1, 128;" ::: "memory");             // whole tile staged
     if (threadIdx.x == 64) TL(6);
-    bool do_epilogue = true;
-    if (split_k > 1) {
+    bool do_epilogue = !cluster_mode;
+    if (split_k > 1 && !cluster_mode) {
       // ---- split-K: publish the partial tile, last-arriving CTA reduces all partials
       const int tile = blockIdx.y * gridDim.x + blockIdx.x;
       const int n_tiles = gridDim.x * gridDim.y;
@@ -341,10 +344,53 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     }
     if (threadIdx.x == 64) TL(7);
     if (do_epilogue) {
-      epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0);
+      epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0, 0, CHUNKS);
     }
     if (threadIdx.x == 64) TL(8);
     (void)m;
+  }
+  if (cluster_mode) {
+    // ---- split-K inside a thread-block cluster (cluster = the split_k CTAs of one output tile):
+    // every CTA has staged its partial tile in its own shared memory; after a cluster barrier
+    // CTA r sums slice r of all partials through distributed shared memory (fixed rank order:
+    // deterministic), applies the fused epilogue to that slice and stores it.  No global
+    // workspace, no atomics, no memory fences.
+    __syncwarp();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp >= 2) {
+      const int et = threadIdx.x - 64;
+      float* stage = reinterpret_cast<float*>(gen_base);
+      const uint32_t stage_u32 = base;
+      const int S = split_k, r = z;                        // cluster spans grid.z: rank == z
+      const int log2S = 31 - __clz(S);
+      const int cpr = (BM * BN / 4) / S;                   // chunks per rank
+      float4 v[CHUNKS];
+#pragma unroll
+      for (int t = 0; t < CHUNKS; ++t) {
+        const int j = t >> log2S, q = t & (S - 1);
+        const int f = r * cpr + j * 128 + et;
+        const uint32_t local = stage_u32 + (uint32_t)(((f >> 4) * SLD + (f & 15) * 4) * 4);
+        uint32_t remote;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(q));
+        asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v[t].x), "=f"(v[t].y), "=f"(v[t].z), "=f"(v[t].w) : "r"(remote) : "memory");
+      }
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int t = 0; t < CHUNKS; ++t) {
+        const int j = t >> log2S, q = t & (S - 1);
+        if (q == 0) acc = v[t];
+        else { acc.x += v[t].x; acc.y += v[t].y; acc.z += v[t].z; acc.w += v[t].w; }
+        if (q == S - 1) {
+          const int f = r * cpr + j * 128 + et;
+          *reinterpret_cast<float4*>(stage + (f >> 4) * SLD + (f & 15) * 4) = acc;     // own slice, own chunks
+        }
+      }
+      epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0, r * cpr, CHUNKS / S);
+    }
+    // peers may still be reading this CTA's shared memory: nobody leaves before everybody is done
+    __syncwarp();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -393,6 +439,7 @@ bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, 
 template <bool A_MN, bool B_MN, int EPI>
 int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
                int vec_ok, cudaStream_t stream) {
+  const int cluster_mode = (ws == nullptr && split_k > 1) ? 1 : 0;   // no workspace given: reduce through DSMEM
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
@@ -400,9 +447,24 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
     attr_done = true;
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
-  k_gemm_tc<A_MN, B_MN, EPI><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr, vec_ok);
   ++g_ftg_launch_count;
-  return (int)cudaPeekAtLastError();
+  if (!cluster_mode) {
+    k_gemm_tc<A_MN, B_MN, EPI><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr, vec_ok, 0);
+    return (int)cudaPeekAtLastError();
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = (unsigned)split_k;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI>, ma, mb, p, split_k, ws, ctr, vec_ok, 1);
 }
 
 template <bool A_MN, bool B_MN>
@@ -458,6 +520,16 @@ extern "C" int ftg_gemm_tc_choose_split(int M, int N, int K) {
   return s;
 }
 
+// Cluster split-K factor: largest power of two <= 8 that keeps >= 2 k-blocks per CTA and the
+// grid within one wave of 148 SMs.
+extern "C" int ftg_gemm_tc_choose_cluster_split(int M, int N, int K) {
+  int tiles = ftg_gemm_tc_num_tiles(M, N);
+  int nkb = ftg_cdiv(K, BK);
+  int s = 1;
+  while (s * 2 <= 8 && tiles * s * 2 <= 148 && nkb / (s * 2) >= 2) s *= 2;
+  return s;
+}
+
 extern "C" int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* workspace, int* tile_counters,
                            ftg_stream_t stream) {
   const ftg_gemm_args& p = *args;
@@ -468,7 +540,12 @@ extern "C" int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* worksp
   const int nkb = ftg_cdiv(p.K, BK);
   if (split_k < 1) split_k = 1;
   if (split_k > nkb) split_k = nkb;
-  if (split_k > 1 && (!workspace || !tile_counters)) return FTG_ERR_UNSUPPORTED;
+  if (split_k > 1 && (!workspace || !tile_counters)) {
+    // cluster (DSMEM) split-K: power-of-two cluster of at most 8 CTAs along K
+    if (split_k > 8 || (split_k & (split_k - 1))) return FTG_ERR_UNSUPPORTED;
+    workspace = nullptr;
+    tile_counters = nullptr;
+  }
   CUtensorMap ma, mb;
   bool ok = p.a_t ? make_map(&ma, p.a, p.M, p.K, p.lda, 32, BK, true) : make_map(&ma, p.a, p.K, p.M, p.lda, BK, BM, false);
   ok = ok && (p.b_t ? make_map(&mb, p.b, p.N, p.K, p.ldb, 32, BK, true) : make_map(&mb, p.b, p.K, p.N, p.ldb, BK, BN, false));

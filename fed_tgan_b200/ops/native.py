@@ -55,6 +55,7 @@ def _sig(name, argtypes, restype=_i):
 _gemm_simt = _sig("ftg_gemm_simt", [C.POINTER(GemmArgs), _vp])
 _gemm_tc = _sig("ftg_gemm_tc", [C.POINTER(GemmArgs), _i, _vp, _vp, _vp])
 _choose_split = _sig("ftg_gemm_tc_choose_split", [_i, _i, _i])
+_choose_cluster_split = _sig("ftg_gemm_tc_choose_cluster_split", [_i, _i, _i])
 _ws_bytes = _sig("ftg_gemm_tc_workspace_bytes", [_i, _i, _i], _ll)
 _num_tiles = _sig("ftg_gemm_tc_num_tiles", [_i, _i])
 _rowdot = _sig("ftg_rowdot", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp])
@@ -134,6 +135,7 @@ def _ld(t):
 
 # ----------------------------------------------------------------- precision
 _precision = os.environ.get("FEDTGAN_PRECISION", "tf32")
+_splitk_mode = os.environ.get("FEDTGAN_SPLITK", "cluster")     # "cluster" (DSMEM) | "workspace"
 _scratch = {}
 MAX_WS_BYTES = 64 << 20
 
@@ -188,14 +190,18 @@ def _gemm_args(a, b, out, a_t, b_t, bias, act, mask_in, mask_out, u, rng, stream
 
 
 def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None, mask_out=None, u=None, rng=None,
-           stream=0, accumulate=False, alpha=1.0, slope=0.2, p=0.5, precision=None, split_k=None):
+           stream=0, accumulate=False, alpha=1.0, slope=0.2, p=0.5, precision=None, split_k=None, splitk_mode=None):
+    splitk_mode = splitk_mode or _splitk_mode
     g = _gemm_args(a, b, out, a_t, b_t, bias, act, mask_in, mask_out, u, rng, stream, accumulate, alpha, slope, p)
     prec = precision or _precision
     st = _stream()
     if prec == "tf32":
-        sk = split_k if split_k is not None else _choose_split(g.M, g.N, g.K)
         ws = ctr = None
-        if sk > 1:
+        if split_k is None and splitk_mode == "cluster":
+            sk = _choose_cluster_split(g.M, g.N, g.K)        # DSMEM reduction inside a cluster: no scratch
+        else:
+            sk = split_k if split_k is not None else _choose_split(g.M, g.N, g.K)
+        if sk > 1 and not (split_k is None and splitk_mode == "cluster"):
             wsb, ctrb = _scratch_for(out.device, st)
             while sk > 1 and _ws_bytes(g.M, g.N, sk) > MAX_WS_BYTES:
                 sk -= 1
