@@ -357,6 +357,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     // workspace, no atomics, no memory fences.
     __syncwarp();
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (threadIdx.x == 64) TL(10);
     if (warp >= 2) {
       const int et = threadIdx.x - 64;
       float* stage = reinterpret_cast<float*>(gen_base);
@@ -386,7 +387,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
           *reinterpret_cast<float4*>(stage + (f >> 4) * SLD + (f & 15) * 4) = acc;     // own slice, own chunks
         }
       }
+      if (threadIdx.x == 64) TL(11);
       epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0, r * cpr, CHUNKS / S);
+      if (threadIdx.x == 64) TL(12);
     }
     // peers may still be reading this CTA's shared memory: nobody leaves before everybody is done
     __syncwarp();

@@ -42,6 +42,32 @@ S_Z_D, S_COL_D, S_OPT_D, S_PERM, S_ROW, S_GUMBEL_D, S_ALPHA, S_DROP_D = range(8)
 S_Z_G, S_COL_G, S_OPT_G, S_GUMBEL_G, S_DROP_G = range(16, 21)
 
 
+class _Branch:
+    """``with engine.branch(k):`` runs the enclosed launches on side stream ``k`` after forking
+    from the current stream; ``engine.join(k)`` makes the current stream wait for them.  In a
+    CUDA-graph capture this turns independent kernels into parallel graph branches."""
+
+    def __init__(self, eng, k):
+        self.eng, self.k, self.ctx = eng, k, None
+
+    def __enter__(self):
+        e = self.eng
+        if not e.concurrent:
+            return self
+        side = e.side_streams[self.k]
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(e.device))
+        side.wait_event(ev)
+        self.ctx = torch.cuda.stream(side)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
+
+
 class TrainEngine:
     def __init__(self, cfg: CTGANConfig, layout: TableLayout, table: DeviceTable | None, device=None,
                  g_arena: GeneratorArena | None = None, d_arena: DiscriminatorArena | None = None,
@@ -56,6 +82,9 @@ class TrainEngine:
         self.D = d_arena if d_arena is not None else DiscriminatorArena(cfg, layout, dev, seed=seed + 1)
         self.rng = ops.RngState(seed, dev)
         self.tables = layout.device_tables(dev)
+        # independent kernels of an iteration run on side streams (parallel graph branches)
+        self.concurrent = dev.type == "cuda"
+        self.side_streams = [torch.cuda.Stream(device=dev) for _ in range(3)] if self.concurrent else []
 
         B, P = cfg.batch_size, cfg.pack
         Bp = B // P
@@ -124,6 +153,15 @@ class TrainEngine:
         self.iterations = 0
 
     # ------------------------------------------------------------------ helpers
+    def branch(self, k):
+        return _Branch(self, k)
+
+    def join(self, k):
+        if self.concurrent:
+            ev = torch.cuda.Event()
+            ev.record(self.side_streams[k])
+            torch.cuda.current_stream(self.device).wait_event(ev)
+
     def _gw(self, l):
         return self.G.view(f"seq.{l}.fc.weight")
 
@@ -207,8 +245,9 @@ class TrainEngine:
         dd = self.layout.data_dim
         dfake = self.dfake[:, :dd]
         hfull = self.h[:, : self.off[0] + self.d0]
-        ops.linear(dfake, hfull, self.G.grad_view(f"seq.{L}.weight"), a_t=True, b_t=True)
-        ops.colsum(dfake, self.G.grad_view(f"seq.{L}.bias"))
+        with self.branch(0):        # weight/bias gradient of the output layer: off the critical path
+            ops.linear(dfake, hfull, self.G.grad_view(f"seq.{L}.weight"), a_t=True, b_t=True)
+            ops.colsum(dfake, self.G.grad_view(f"seq.{L}.bias"))
         dh = self.dh[:, : self.sum_h]
         ops.linear(dfake, self.G.view(f"seq.{L}.weight")[:, : self.sum_h], dh, b_t=True)
         for l in range(L, 0, -1):
@@ -220,11 +259,16 @@ class TrainEngine:
                 dbias_fc=self.G.grad_view(f"seq.{l - 1}.fc.bias"),
             )
             x = self.h[:, hi: self.off[0] + self.d0]
-            ops.linear(self.da[l - 1], x, self.G.grad_view(f"seq.{l - 1}.fc.weight"), a_t=True, b_t=True)
             if l > 1:
+                with self.branch(1):    # wgrad in parallel with the dgrad that feeds the next layer
+                    ops.linear(self.da[l - 1], x, self.G.grad_view(f"seq.{l - 1}.fc.weight"), a_t=True, b_t=True)
                 width = self.sum_h - hi      # columns of W_l that multiply r_{l-1}..r_1
                 ops.linear(self.da[l - 1], self._gw(l - 1)[:, :width], dh[:, hi: self.sum_h], b_t=True,
                            accumulate=True)
+            else:
+                ops.linear(self.da[l - 1], x, self.G.grad_view(f"seq.{l - 1}.fc.weight"), a_t=True, b_t=True)
+        self.join(0)
+        self.join(1)
 
     # ------------------------------------------------------------ discriminator
     def d_forward(self, rows, inject, key, stream, rowscale=None, loss_out=None):
@@ -251,13 +295,20 @@ class TrainEngine:
             ops.linear(self.Z[l][:rows], self._dw(l), self.Z[l - 1][:rows], b_t=True, mask_in=self.Mask[l - 1][:rows])
 
     # ------------------------------------------------------------------- steps
-    def d_step(self, inject=None):
+    def d_step(self, inject=None, prefetch_g=False):
         cfg, B, Bp = self.cfg, self.B, self.Bp
         dd, n_opt, din = self.layout.data_dim, self.layout.n_opt, self.din
         c1 = self._prep(inject, "d", with_real=True)
         self.g_forward(training=True)
         ops.activate_fwd(self.fake, self.tables, self.X[:B], tau=cfg.tau, u=self._rand(inject, "u_gumbel_d", None),
                          rng=self.rng, stream=S_GUMBEL_D, cond=c1)
+        if prefetch_g:
+            # The G step's batch preparation and generator forward only depend on buffers this D
+            # step is done with (h, a, fake) and on G's weights, which the D step never changes:
+            # run them on a side stream underneath the discriminator's forward/backward.
+            with self.branch(2):
+                self._g_c1 = self._prep(inject, "g", with_real=False)
+                self.g_forward(training=True)
         ops.slerp(self.X[B:2 * B, :din], self.X[:B, :din], self.X[2 * B:, :din],
                   alpha=self._rand(inject, "alpha", None), rng=self.rng, stream=S_ALPHA)
         self.d_forward(3 * Bp, inject, "u_drop_d", S_DROP_D, self.rowscale_loss, self.loss_d)   # + WGAN loss value
@@ -273,23 +324,35 @@ class TrainEngine:
         for l in range(nl):
             ops.linear(src, self._dw(l), self.Lact[l][I], mask_in=self.Mask[l][I])
             src = self.Lact[l][I]
-        # weight gradients: WGAN rows and penalty rows stacked along K
-        inp = self.Xp
-        for l in range(nl):
-            ops.linear(self.Z[l], inp, self.D.grad_view(f"{self.D.layer_keys[l]}.weight"), a_t=True, b_t=True)
-            ops.colsum(self.Z[l][:2 * Bp], self.D.grad_view(f"{self.D.layer_keys[l]}.bias"))
-            inp = self.Lact[l]
-        ops.colsum(self.Lact[nl - 1], self.D.grad_view(f"{self.D.layer_keys[nl]}.weight").view(-1),
-                   rowscale=self.rowscale_d)
+        # weight gradients: WGAN rows and penalty rows stacked along K; the per-layer GEMMs and the
+        # bias / head reductions are independent of each other -> parallel branches
+        with self.branch(0):
+            inp = self.Xp
+            for l in range(nl):
+                if l > 0:
+                    ops.linear(self.Z[l], inp, self.D.grad_view(f"{self.D.layer_keys[l]}.weight"), a_t=True, b_t=True)
+                inp = self.Lact[l]
+        with self.branch(1):
+            for l in range(nl):
+                ops.colsum(self.Z[l][:2 * Bp], self.D.grad_view(f"{self.D.layer_keys[l]}.bias"))
+            ops.colsum(self.Lact[nl - 1], self.D.grad_view(f"{self.D.layer_keys[nl]}.weight").view(-1),
+                       rowscale=self.rowscale_d)
+        ops.linear(self.Z[0], self.Xp, self.D.grad_view(f"{self.D.layer_keys[0]}.weight"), a_t=True, b_t=True)
+        self.join(0)
+        self.join(1)
         # d loss_d / d b_head = sum(rowscale over fake+real) = 0 exactly: its grad slot stays 0
         ops.adam_step(self.D.data[: self.D.n_trainable], self.D.grad, self.D.exp_avg, self.D.exp_avg_sq,
                       self.rng.state[1:2], lr=cfg.lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.adam_eps)
 
-    def g_step(self, inject=None):
+    def g_step(self, inject=None, prefetched=False):
         cfg, B, Bp = self.cfg, self.B, self.Bp
         dd = self.layout.data_dim
-        c1 = self._prep(inject, "g", with_real=False)
-        self.g_forward(training=True)
+        if prefetched:
+            self.join(2)
+            c1 = self._g_c1
+        else:
+            c1 = self._prep(inject, "g", with_real=False)
+            self.g_forward(training=True)
         ops.activate_fwd(self.fake, self.tables, self.X[:B], tau=cfg.tau, u=self._rand(inject, "u_gumbel_g", None),
                          rng=self.rng, stream=S_GUMBEL_G, cond=c1)
         self.d_forward(Bp, inject, "u_drop_g", S_DROP_G, self.rowscale_g, self.loss_g_adv)
@@ -304,8 +367,9 @@ class TrainEngine:
 
     def iteration(self, inject=None):
         self.rng.tick()
-        self.d_step(inject)
-        self.g_step(inject)
+        overlap = self.concurrent
+        self.d_step(inject, prefetch_g=overlap)
+        self.g_step(inject, prefetched=overlap)
         self.iterations += 1
 
     def train(self, steps: int):

@@ -15,7 +15,7 @@ lib = native.lib
 lib.ftg_gemm_tc_timeline.argtypes = [C.c_int, C.POINTER(C.c_longlong)]
 dev = torch.device("cuda:0")
 names = ["start", "prod_begin", "prod_end", "mma_first_full", "mma_commit", "epi_tmem_full", "epi_staged", "epi_begin",
-         "epi_end", "exit"]
+         "epi_end", "exit", "cl_bar1", "cl_reduced", "cl_epi_done"]
 shapes = [(500, 256, 252, 0, 0, None), (500, 256, 508, 0, 0, None), (150, 256, 2520, 0, 0, None),
           (150, 256, 2520, 0, 0, 1), (50, 2520, 256, 0, 1, None), (256, 2520, 150, 1, 1, None), (500, 128, 764, 0, 0, None),
           (8192, 256, 508, 0, 0, None)]
@@ -34,7 +34,7 @@ for M, N, K, at, bt, sk in shapes:
     torch.cuda.synchronize()
     buf = (C.c_longlong * 16)()
     lib.ftg_gemm_tc_timeline(0, buf)
-    t = list(buf)[:10]
+    t = list(buf)[:13]
     rel = {n: t[i] - t[0] for i, n in enumerate(names)}
     # graph-replayed latency (no host overhead)
     g = torch.cuda.CUDAGraph()
