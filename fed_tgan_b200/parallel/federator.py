@@ -77,7 +77,8 @@ class MDGANServer:
         self.seed = self.cfg.seed if seed is None else seed
         self.np_rng = np.random.default_rng(self.seed + 99)
         self.metrics = MetricsLog(os.path.join(out_dir, "metrics.jsonl") if self.group.is_root else None)
-        self._writer = ThreadPoolExecutor(max_workers=2) if async_csv else None
+        self._writer = ThreadPoolExecutor(max_workers=3) if async_csv else None
+        self._slots = None
         self._pending = []
         self.start_epoch = 0
         self.round_times = []
@@ -224,11 +225,76 @@ class MDGANServer:
         write_table_csv(path, names, cols)
         return path
 
+    # ---- asynchronous generation pipeline (device path) --------------------------------
+    def _async_setup(self, arena):
+        from ..models.arena import GeneratorArena
+
+        dev = arena.device
+        self._gen_stream = torch.cuda.Stream(device=dev)
+        self._snap = GeneratorArena(self.cfg, self.layout, dev, init=False)
+        n, ncol = self.cfg.sample_rows, int(np.asarray(self.decode_tables["col_is_cont"]).size)
+        self._slots = [{"dev": torch.empty(n, ncol, dtype=torch.float32, device=dev),
+                        "host": torch.empty(n, ncol, dtype=torch.float32).pin_memory(),
+                        "done": torch.cuda.Event(), "future": None} for _ in range(3)]
+        self._slot_i = 0
+        self._gen_graph = None
+
+    def _sample_data_async(self, index):
+        """Snapshot G, then generate + copy to pinned host memory on a side stream (one CUDA
+        graph) while the caller goes on with the next round; a worker thread waits for the
+        copy and writes the CSV."""
+        arena = self.group.generator_arena()
+        if getattr(self, "_slots", None) is None:
+            self._async_setup(arena)
+        slot = self._slots[self._slot_i]
+        self._slot_i = (self._slot_i + 1) % len(self._slots)
+        if slot["future"] is not None:
+            slot["future"].result()                 # the slot's previous CSV is on disk
+        cur = torch.cuda.current_stream(arena.device)
+        gen = self._row_generator(arena.device)
+        self._gen_stream.wait_stream(cur)
+        with torch.cuda.stream(self._gen_stream):
+            self._snap.data.copy_(arena.data, non_blocking=True)
+            if self._gen_graph is None:
+                from ..ops import native
+
+                native.preallocate_scratch(arena.device)
+                gen.generate(self._snap, self.cfg.sample_rows, out=self._slots[0]["dev"])      # warm-up, uncaptured
+                self._gen_stream.synchronize()
+                self._gen_graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._gen_graph, stream=self._gen_stream):
+                    gen.generate(self._snap, self.cfg.sample_rows, out=self._gen_out())
+            self._gen_graph.replay()
+            slot["dev"].copy_(self._gen_out(), non_blocking=True)
+            slot["host"].copy_(slot["dev"], non_blocking=True)
+            slot["done"].record(self._gen_stream)
+        self.d2h_bytes_last = slot["host"].numel() * 4
+
+        def finish(slot=slot, index=index):
+            slot["done"].synchronize()
+            if self.write_csv:
+                return self._decode_and_write(slot["host"].numpy(), index)
+            return None
+
+        slot["future"] = self._writer.submit(finish)
+        self._pending = [f for f in self._pending if not f.done()]
+        self._pending.append(slot["future"])
+        return None
+
+    def _gen_out(self):
+        if getattr(self, "_gen_out_buf", None) is None:
+            s0 = self._slots[0]["dev"]
+            self._gen_out_buf = torch.empty_like(s0)
+        return self._gen_out_buf
+
     def sample_data(self, index, wait=True):
         """Generate ``cfg.sample_rows`` rows with the current global G and write
         ``<Name>_result/<Name>_synthesis_epoch_<index>.csv`` (reference ``:582-590``)."""
         if not self.group.is_root:
             return None
+        if (not wait and self._writer is not None and self.group.generator_arena().device.type == "cuda"
+                and self.group.__class__.__name__ != "RpcGroup"):
+            return self._sample_data_async(index)
         t0 = time.time()
         dev_table = self.sample(self.cfg.sample_rows)
         host = torch.empty(dev_table.shape, dtype=dev_table.dtype, pin_memory=dev_table.is_cuda)
