@@ -31,6 +31,17 @@ int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* n
     for (const char* p = s; *p; ++p) { if (*p == '"') out.push_back('"'); out.push_back(*p); }
     out.push_back('"');
   };
+  auto put_float = [](std::string& out, float v) {
+    if (std::isnan(v)) return;
+    if (std::isinf(v)) { out.append(v > 0 ? "inf" : "-inf"); return; }
+    char tmp[24];
+    auto res = std::to_chars(tmp, tmp + sizeof(tmp), v);      // shortest string that round-trips the float32
+    bool plain = true;
+    for (char* p = tmp; p < res.ptr; ++p)
+      if (*p == '.' || *p == 'e') { plain = false; break; }
+    out.append(tmp, res.ptr - tmp);
+    if (plain) out.append(".0");
+  };
   auto put_double = [](std::string& out, double v) {
     if (std::isnan(v)) return;                        // pandas writes NaN as empty
     if (std::isinf(v)) { out.append(v > 0 ? "inf" : "-inf"); return; }
@@ -45,13 +56,13 @@ int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* n
   auto work = [&](int t) {
     long long r0 = (long long)n_rows * t / n_threads, r1 = (long long)n_rows * (t + 1) / n_threads;
     std::string& out = bufs[t];
-    out.reserve((size_t)(r1 - r0) * n_cols * 12);
+    out.reserve((size_t)(r1 - r0) * n_cols * 14);
     for (long long r = r0; r < r1; ++r) {
       for (int c = 0; c < n_cols; ++c) {
         if (c) out.push_back(',');
         switch (kinds[c]) {
           case 0: put_double(out, static_cast<const double*>(columns[c])[r]); break;
-          case 1: put_double(out, (double)static_cast<const float*>(columns[c])[r]); break;
+          case 1: put_float(out, static_cast<const float*>(columns[c])[r]); break;
           case 2: {
             char tmp[24];
             auto res = std::to_chars(tmp, tmp + sizeof(tmp), static_cast<const int64_t*>(columns[c])[r]);

@@ -68,7 +68,8 @@ class Transform:
                 else:
                     cols.append(y)
             else:
-                cols.append(raw.astype(np.float64))
+                # generated values carry float32 precision: keep them float32 on the fast path
+                cols.append(np.ascontiguousarray(raw) if (as_codes and raw.dtype == np.float32) else raw.astype(np.float64))
         return names, cols
 
     @staticmethod

@@ -65,7 +65,7 @@ def write_csv(path, names, cols, n_threads=None):
                 raise TypeError(f"column {names[i]}: unsupported dtype {arr.dtype}")
             keep.append(arr)
             ptrs[i] = arr.ctypes.data
-    nt = n_threads or min(8, os.cpu_count() or 1)
+    nt = n_threads or min(4, os.cpu_count() or 1)   # several CSVs are in flight at once (writer pool)
     rc = lib.ftg_csv_write(str(path).encode(), n_rows, n_cols, c_names, kinds, ptrs, tables, nt)
     if rc != 0:
         raise OSError(f"ftg_csv_write({path}) failed: {rc}")

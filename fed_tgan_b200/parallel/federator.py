@@ -77,7 +77,7 @@ class MDGANServer:
         self.seed = self.cfg.seed if seed is None else seed
         self.np_rng = np.random.default_rng(self.seed + 99)
         self.metrics = MetricsLog(os.path.join(out_dir, "metrics.jsonl") if self.group.is_root else None)
-        self._writer = ThreadPoolExecutor(max_workers=3) if async_csv else None
+        self._writer = ThreadPoolExecutor(max_workers=6) if async_csv else None
         self._slots = None
         self._pending = []
         self.start_epoch = 0
@@ -235,7 +235,7 @@ class MDGANServer:
         n, ncol = self.cfg.sample_rows, int(np.asarray(self.decode_tables["col_is_cont"]).size)
         self._slots = [{"dev": torch.empty(n, ncol, dtype=torch.float32, device=dev),
                         "host": torch.empty(n, ncol, dtype=torch.float32).pin_memory(),
-                        "done": torch.cuda.Event(), "future": None} for _ in range(3)]
+                        "done": torch.cuda.Event(), "future": None} for _ in range(8)]
         self._slot_i = 0
         self._gen_graph = None
 
