@@ -96,6 +96,10 @@ __device__ __forceinline__ bool wait_peers(const Peers& P, int rank, int world, 
 }
 
 // ----------------------------------------------------------------- two-shot
+// W = compile-time upper bound of the world size, U = float4 chunks per thread per trip:
+// W * U = 16 independent 16 B peer loads in flight per thread (NVLink latency ~2 us needs
+// >1 MB in flight per GPU to approach link bandwidth).
+template <int W, int U>
 __global__ void __launch_bounds__(256)
 k_fedavg_twoshot(Peers P, int rank, int world, long long n4, IntSlots slots, int round_id, int* status,
                  unsigned long long timeout_ns) {
@@ -113,23 +117,33 @@ k_fedavg_twoshot(Peers P, int rank, int world, long long n4, IntSlots slots, int
   // reduce-scatter + all-gather of shard `rank`, element by element, in place
   const long long chunk = (n4 + world - 1) / world;
   const long long lo = (long long)rank * chunk, hi = min(n4, lo + chunk);
-  for (long long q = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q < hi; q += (long long)gridDim.x * blockDim.x) {
-    float4 v[MAX_WORLD];
+  const long long T = (long long)gridDim.x * blockDim.x;
+  for (long long q0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < hi; q0 += T * U) {
+    float4 v[U][W];
 #pragma unroll
-    for (int i = 0; i < MAX_WORLD; ++i)
-      if (i < world) v[i] = reinterpret_cast<const float4*>(P.p[i])[q];       // peer loads over NVLink
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int u = 0; u < U; ++u) {
+      const long long q = q0 + u * T;
 #pragma unroll
-    for (int i = 0; i < MAX_WORLD; ++i)
-      if (i < world) {
-        float w = P.w[i];
-        acc.x = fmaf(w, v[i].x, acc.x); acc.y = fmaf(w, v[i].y, acc.y);
-        acc.z = fmaf(w, v[i].z, acc.z); acc.w = fmaf(w, v[i].w, acc.w);
-      }
-    if (slots.n) acc = trunc_slots(acc, q * 4, slots);
+      for (int i = 0; i < W; ++i)
+        if (i < world && q < hi) v[u][i] = reinterpret_cast<const float4*>(P.p[i])[q];   // peer loads over NVLink
+    }
 #pragma unroll
-    for (int i = 0; i < MAX_WORLD; ++i)
-      if (i < world) reinterpret_cast<float4*>(P.p[i])[q] = acc;              // peer stores over NVLink
+    for (int u = 0; u < U; ++u) {
+      const long long q = q0 + u * T;
+      if (q >= hi) continue;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int i = 0; i < W; ++i)
+        if (i < world) {
+          const float w = P.w[i];
+          acc.x = fmaf(w, v[u][i].x, acc.x); acc.y = fmaf(w, v[u][i].y, acc.y);
+          acc.z = fmaf(w, v[u][i].z, acc.z); acc.w = fmaf(w, v[u][i].w, acc.w);
+        }
+      if (slots.n) acc = trunc_slots(acc, q * 4, slots);
+#pragma unroll
+      for (int i = 0; i < W; ++i)
+        if (i < world) reinterpret_cast<float4*>(P.p[i])[q] = acc;                        // peer stores over NVLink
+    }
   }
   // barrier-out: all my stores are visible system-wide before peers may continue
   __threadfence_system();
@@ -239,11 +253,16 @@ extern "C" int ftg_fedavg_twoshot(float* const* peers, int* const* flags, int ra
   if (n & 3) return FTG_ERR_UNSUPPORTED;
   long long n4 = n / 4;
   long long per = (n4 + world - 1) / world;
-  int blocks = ftg_cdiv(per, 256);
-  if (blocks > 128) blocks = 128;          // all CTAs co-resident (they meet at the exit barrier)
+  const int U = world <= 2 ? 8 : world <= 4 ? 4 : world <= 8 ? 2 : 1;
+  int blocks = ftg_cdiv(per, 256 * U);
+  if (blocks > 144) blocks = 144;          // all CTAs co-resident (they meet at the exit barrier)
   if (blocks < 1) blocks = 1;
-  k_fedavg_twoshot<<<blocks, 256, 0, (cudaStream_t)stream>>>(P, rank, world, n4, S, round_id, status,
-                                                             (unsigned long long)timeout_ms * 1000000ull);
+  const unsigned long long tns = (unsigned long long)timeout_ms * 1000000ull;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (world <= 2) k_fedavg_twoshot<2, 8><<<blocks, 256, 0, st>>>(P, rank, world, n4, S, round_id, status, tns);
+  else if (world <= 4) k_fedavg_twoshot<4, 4><<<blocks, 256, 0, st>>>(P, rank, world, n4, S, round_id, status, tns);
+  else if (world <= 8) k_fedavg_twoshot<8, 2><<<blocks, 256, 0, st>>>(P, rank, world, n4, S, round_id, status, tns);
+  else k_fedavg_twoshot<16, 1><<<blocks, 256, 0, st>>>(P, rank, world, n4, S, round_id, status, tns);
   FTG_LAUNCH_CHECK();
   return 0;
 }

@@ -49,6 +49,22 @@ def _pick_device(device=None):
     return torch.device("cpu")
 
 
+def _on_device(fn):
+    """RPC handlers run on arbitrary worker threads whose current CUDA device is 0: make the
+    client's own GPU current for the duration of the call (streams, graphs and the native
+    library all follow the current device)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(self, *a, **k):
+        if self.device.type == "cuda":
+            with torch.cuda.device(self.device):
+                return fn(self, *a, **k)
+        return fn(self, *a, **k)
+
+    return wrapper
+
+
 class MDGANClient:
     def __init__(self, datapath, selected_variables, categorical_list, nonnegative_list, date_dic, target_column,
                  problem_type, epochs, device=None, config: CTGANConfig | dict | None = None, dataframe=None,
@@ -99,6 +115,7 @@ class MDGANClient:
             dataframe=self._dataframe, write_side_files=self.write_side_files)
         self.rows = self.train.shape[0]
 
+    @_on_device
     def get_transformer_information(self):
         """Encode with the global label encoders, fit local per-column mixtures and return
         ``(models, component masks, transformer meta, n_rows)``."""
@@ -118,6 +135,7 @@ class MDGANClient:
         self.components = components
         return True
 
+    @_on_device
     def refit_transformer(self):
         """Adopt the global encoders, encode the shard, build sampler tables, networks and
         optimiser state (reference ``:295-317``)."""
@@ -157,24 +175,30 @@ class MDGANClient:
                 "n_col": self.layout.n_col, "n_opt": self.layout.n_opt}
 
     # ----------------------------------------------------------------- weights
+    @_on_device
     def get_models(self):
         """Reference-layout CPU modules (``ctgan.Generator``, ``ctgan.Discriminator``)."""
         return self.engine.G.to_module(), self.engine.D.to_module()
 
+    @_on_device
     def get_state_dicts(self):
         return ({k: v.cpu() for k, v in self.engine.G.state_dict().items()},
                 {k: v.cpu() for k, v in self.engine.D.state_dict().items()})
 
+    @_on_device
     def get_discriminator_weights(self):
         return {k: v.cpu() for k, v in self.engine.D.state_dict().items()}
 
+    @_on_device
     def get_generator_weights(self):
         return {k: v.cpu() for k, v in self.engine.G.state_dict().items()}
 
+    @_on_device
     def set_discriminator_weights(self, state_dict):
         self.engine.D.load_state_dict(state_dict)
         return True
 
+    @_on_device
     def set_generator_weights(self, state_dict):
         self.engine.G.load_state_dict(state_dict)
         return True
@@ -183,6 +207,7 @@ class MDGANClient:
         return True   # arenas never leave the device
 
     # ------------------------------------------------------------------ training
+    @_on_device
     def run_local_epochs(self, number_of_epoch=1, use_graph=None):
         """Local training without any host read-back (the hot path)."""
         steps = int(number_of_epoch) * self.steps_per_epoch
@@ -200,11 +225,13 @@ class MDGANClient:
             self.engine.train(steps)
         return steps
 
+    @_on_device
     def train_model(self, number_of_epoch=1):
         """Reference API: train ``number_of_epoch`` local epochs and return CPU state_dicts."""
         self.run_local_epochs(number_of_epoch)
         return self.get_state_dicts()
 
+    @_on_device
     def get_losses(self):
         return self.engine.losses() if self.engine is not None else {}
 
@@ -213,6 +240,7 @@ class MDGANClient:
         self.last_losses = self.get_losses()
         return self.last_losses
 
+    @_on_device
     def restage_shard(self):
         """Host(pinned)->device copy of this client's compact shard (out-of-core / e2e path)."""
         return self.table.restage()
@@ -224,6 +252,7 @@ class MDGANClient:
         return self._graph.launches_per_replay if self._graph is not None else 0
 
     # --------------------------------------------------------------- checkpoint
+    @_on_device
     def checkpoint_state(self):
         e = self.engine
         return {
@@ -233,6 +262,7 @@ class MDGANClient:
             "rng": e.rng.state.cpu().clone(), "iterations": e.iterations,
         }
 
+    @_on_device
     def load_checkpoint_state(self, st):
         e = self.engine
         e.G.load_state_dict(st["G"])
@@ -244,6 +274,7 @@ class MDGANClient:
         return True
 
     # ------------------------------------------------- symmetric memory (GPU only)
+    @_on_device
     def symm_export(self):
         """Allocate the peer-visible arena block and return its IPC handle bytes."""
         from .symm import SymmetricBlock
@@ -259,16 +290,20 @@ class MDGANClient:
         self.engine.D.data.copy_(d_old)
         return self.symm.export_handle()
 
+    @_on_device
     def symm_connect(self, rank, handles):
         self.symm.connect(rank, handles)
         return True
 
-    def symm_aggregate(self, weights, round_id):
+    @_on_device
+    def symm_aggregate(self, weights, round_id, sync=False):
         """Launch the fused weighted all-reduce on this client's GPU (all clients must be
         launched concurrently; they synchronise inside the kernel over NVLink)."""
         e = self.engine
         ints = [o for o in e.G.int_slot_offsets()]
         self.symm.fedavg(weights, e.G.numel + e.D.numel, ints, round_id)
+        if sync:
+            self.symm.check()        # raises if a peer never arrived at the in-kernel barrier
         return True
 
     # ------------------------------------- legacy MD-GAN / GDTS split-training API
@@ -297,6 +332,7 @@ class MDGANClient:
         timings.append(time.time() - t0)
         return out, fakeact
 
+    @_on_device
     def train_D(self):
         """MD-GAN mode: the generator lives on the server, D is trained here (``:421-480``)."""
         self._legacy_setup()
@@ -320,6 +356,7 @@ class MDGANClient:
             self.optD.step()
         return loss_d.detach().cpu(), pen.detach().cpu()
 
+    @_on_device
     def loss_G(self):
         """MD-GAN mode: generator loss evaluated against the local D (``:483-525``)."""
         self._legacy_setup()

@@ -140,7 +140,7 @@ class RpcGroup(ClientGroup):
         if self.n == 1:
             return
         if self.use_symmetric:
-            self.call("symm_aggregate", list(map(float, weights)), int(round_id))
+            self.call("symm_aggregate", list(map(float, weights)), int(round_id), True)
             return
         # CPU / no-peer-access path == the reference's data flow (gather, average, push)
         pairs = self.call("get_state_dicts")

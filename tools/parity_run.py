@@ -1,0 +1,102 @@
+"""Statistical parity: Avg_JSD / Avg_WD per epoch, ours vs the unmodified reference, same
+synthetic table and IID split, 2 clients, both arms on one GPU.  Writes
+gpurun_out/parity_<config>.json.
+
+    python tools/parity_run.py [epochs] [config] [seeds]
+"""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "baseline"))
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from fed_tgan_b200.config import CTGANConfig  # noqa: E402
+from fed_tgan_b200.data.schemas import get_schema, make_table, split_table  # noqa: E402
+from fed_tgan_b200.eval import stat_sim_normalize  # noqa: E402
+from fed_tgan_b200.parallel.client import MDGANClient  # noqa: E402
+from fed_tgan_b200.parallel.federator import MDGANServer  # noqa: E402
+from fed_tgan_b200.parallel.launcher import federate  # noqa: E402
+import ref_harness  # noqa: E402
+
+epochs = int(sys.argv[1]) if len(sys.argv) > 1 else 10
+config = sys.argv[2] if len(sys.argv) > 2 else "adult"
+seeds = int(sys.argv[3]) if len(sys.argv) > 3 else 2
+n_clients = 2
+schema = get_schema(config)
+df = make_table(schema, seed=0)
+shards = split_table(df, n_clients, "iid", seed=0)
+dev = "cuda:0" if torch.cuda.is_available() else "cpu"
+out = {"config": config, "epochs": epochs, "clients": n_clients, "rows": len(df), "ours": [], "reference": []}
+
+
+def curves(result_dir, name):
+    res = []
+    for i in range(epochs):
+        p = os.path.join(result_dir, f"{name}_synthesis_epoch_{i}.csv")
+        res.append(stat_sim_normalize(df, p, schema.categorical))
+    return res
+
+
+for seed in range(seeds):
+    # ---------------- ours
+    base = tempfile.mkdtemp(prefix="parity_ours_")
+    cfg = CTGANConfig(seed=seed)
+    t0 = time.time()
+    clients = [MDGANClient(datapath=f"{schema.name}_train.csv", selected_variables=schema.columns,
+                           categorical_list=schema.categorical, nonnegative_list=schema.nonnegative, date_dic={},
+                           target_column=schema.target, problem_type="", epochs=epochs, device=dev, config=cfg,
+                           dataframe=sh, write_side_files=False, client_id=i, vgm_backend="sklearn")
+               for i, sh in enumerate(shards)]
+    server = MDGANServer(clients, epochs=epochs, config=cfg, name=schema.name, out_dir=base, device=dev)
+    federate(server, verbose=False)
+    c = curves(os.path.join(base, f"{schema.name}_result"), schema.name)
+    out["ours"].append({"seed": seed, "wall_s": round(time.time() - t0, 1), "avg_jsd": [x[0] for x in c],
+                        "avg_wd": [x[1] for x in c], "round_s": server.round_times,
+                        "weights": [float(w) for w in server.weights_con_cat_combination]})
+    print("ours seed", seed, "final JSD/WD", c[-1], flush=True)
+
+for seed in range(seeds):
+    # ---------------- reference (its own run(); torch/numpy seeds are whatever it draws)
+    base = tempfile.mkdtemp(prefix="parity_ref_")
+    ref_harness._prepare_dirs(base, schema, df, shards)
+    common = dict(world_size=n_clients + 1, port=24500 + seed, columns=schema.columns, categorical=schema.categorical,
+                  nonnegative=schema.nonnegative, target=schema.target, epochs=epochs)
+    t0 = time.time()
+    procs = [ref_harness._spawn(dict(common, rank=0, cwd=os.path.join(base, "server")), None, os.path.join(base, "server.log"))]
+    for i in range(n_clients):
+        procs.append(ref_harness._spawn(dict(common, rank=i + 1, cwd=os.path.join(base, f"client{i + 1}")),
+                                        0 if dev != "cpu" else None, os.path.join(base, f"client{i + 1}.log")))
+    rc = [p.wait() for p in procs]
+    if any(rc):
+        print("reference failed", rc, open(os.path.join(base, "server.log")).read()[-2000:])
+        continue
+    c = curves(os.path.join(base, "server", "Intrusion_result"), "Intrusion")
+    times = [float(x) for x in open(os.path.join(base, "server", "timestamp_experiment.csv")).read().split()]
+    out["reference"].append({"seed": seed, "wall_s": round(time.time() - t0, 1), "avg_jsd": [x[0] for x in c],
+                             "avg_wd": [x[1] for x in c], "round_s": times})
+    print("reference seed", seed, "final JSD/WD", c[-1], flush=True)
+
+
+def summary(arm):
+    if not out[arm]:
+        return None
+    j = np.array([r["avg_jsd"] for r in out[arm]])
+    w = np.array([r["avg_wd"] for r in out[arm]])
+    return {"final_avg_jsd_mean": float(j[:, -1].mean()), "final_avg_jsd_std": float(j[:, -1].std()),
+            "final_avg_wd_mean": float(w[:, -1].mean()), "final_avg_wd_std": float(w[:, -1].std()),
+            "epoch0_avg_jsd": float(j[:, 0].mean()), "epoch0_avg_wd": float(w[:, 0].mean()),
+            "mean_round_s": float(np.mean([np.mean(r["round_s"][1:]) for r in out[arm]]))}
+
+
+out["summary"] = {"ours": summary("ours"), "reference": summary("reference")}
+os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"parity_{config}.json"), "w"), indent=1)
+print(json.dumps(out["summary"], indent=1))
