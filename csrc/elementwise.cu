@@ -219,6 +219,58 @@ extern "C" int ftg_rowdot(const float* a, int lda, int M, int K, const float* w,
   return 0;
 }
 
+// Discriminator head, forward + first backward signal in ONE launch:
+//   block 0      : y[m] = a[m,:].w + bias ; loss = sum_m rs_loss[m] * y[m]
+//   blocks 1..   : Z[m,n] = rs_sig[m] * w[n] * mask[m,n]      (d loss / d pre-activation of the last hidden layer)
+__global__ void __launch_bounds__(1024) k_d_head(const float* __restrict__ a, int lda, int M, int K,
+                                                 const float* __restrict__ w, const float* bias, float* y,
+                                                 const float* __restrict__ rs_loss, float* loss_out,
+                                                 const float* __restrict__ rs_sig, const float* __restrict__ mask,
+                                                 int ldm, float* Z, int ldz) {
+  if (blockIdx.x == 0) {
+    __shared__ float red[32];
+    const int sub = threadIdx.x & 7, rloc = threadIdx.x >> 3, rpp = blockDim.x >> 3;
+    float contrib = 0.f;
+    for (int row0 = 0; row0 < M; row0 += rpp) {
+      const int row = row0 + rloc;
+      float s = 0.f;
+      if (row < M) {
+        const float* ar = a + (size_t)row * lda;
+#pragma unroll 4
+        for (int k = sub; k < K; k += 8) s += ar[k] * __ldg(w + k);
+      }
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      s += __shfl_xor_sync(0xffffffffu, s, 4);
+      if (row < M && sub == 0) {
+        s += bias ? bias[0] : 0.f;
+        y[row] = s;
+        contrib += rs_loss[row] * s;
+      }
+    }
+    const float tot = block_sum(contrib, red);
+    if (threadIdx.x == 0) loss_out[0] = tot;
+  } else {
+    const long long total = (long long)M * K;
+    for (long long e = (long long)(blockIdx.x - 1) * blockDim.x + threadIdx.x; e < total;
+         e += (long long)(gridDim.x - 1) * blockDim.x) {
+      const int m = (int)(e / K), n = (int)(e % K);
+      Z[(size_t)m * ldz + n] = rs_sig[m] * __ldg(w + n) * mask[(size_t)m * ldm + n];
+    }
+  }
+}
+
+extern "C" int ftg_d_head(const float* a, int lda, int M, int K, const float* w, const float* bias, float* y,
+                          const float* rs_loss, float* loss_out, const float* rs_sig, const float* mask, int ldm,
+                          float* Z, int ldz, ftg_stream_t stream) {
+  int extra = ftg_cdiv((long long)M * K, 1024 * 4);
+  if (extra < 1) extra = 1;
+  k_d_head<<<1 + extra, 1024, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, y, rs_loss, loss_out, rs_sig, mask, ldm,
+                                                        Z, ldz);
+  FTG_LAUNCH_CHECK();
+  return 0;
+}
+
 extern "C" int ftg_rowdot_loss(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
                                const float* rowscale, float* loss_out, ftg_stream_t stream) {
   k_rowdot<<<1, 1024, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, out, rowscale, loss_out);

@@ -271,9 +271,9 @@ class TrainEngine:
         self.join(1)
 
     # ------------------------------------------------------------ discriminator
-    def d_forward(self, rows, inject, key, stream, rowscale=None, loss_out=None):
-        """Forward rows ``[0:rows)`` of the packed batch; fills Lact/Mask/y (and the fused
-        scalar ``loss_out = sum rowscale * y``)."""
+    def d_forward(self, rows, inject, key, stream, rowscale=None, loss_out=None, rs_sig=None):
+        """Forward rows ``[0:rows)`` of the packed batch; fills Lact/Mask/y, the fused scalar
+        ``loss_out = sum rowscale * y`` and the head's backward signal ``Z_{L-1}``."""
         cfg = self.cfg
         x = self.Xp[:rows]
         for l, hl in enumerate(self.dhid):
@@ -285,12 +285,12 @@ class TrainEngine:
                        slope=cfg.leaky_slope, p=cfg.dropout_p)
             x = self.Lact[l][:rows]
         nl = len(self.dhid)
-        ops.rowdot(x, self._dw(nl), self._db(nl), self.y[:rows], rowscale=rowscale, loss_out=loss_out)
+        ops.d_head(x, self._dw(nl), self._db(nl), self.y[:rows], rowscale, loss_out, rs_sig,
+                   self.Mask[nl - 1][:rows], self.Z[nl - 1][:rows])
 
     def d_signals(self, rows, rowscale):
         """Backward signals ``Z_l = dLoss/d(pre-activation_l)`` for ``loss = sum rowscale*y``."""
-        nl = len(self.dhid)
-        ops.scale_outer_mask(rowscale, self._dw(nl), self.Mask[nl - 1][:rows], self.Z[nl - 1][:rows])
+        nl = len(self.dhid)                 # Z[nl-1] was produced by d_head inside d_forward
         for l in range(nl - 1, 0, -1):
             ops.linear(self.Z[l][:rows], self._dw(l), self.Z[l - 1][:rows], b_t=True, mask_in=self.Mask[l - 1][:rows])
 
@@ -311,7 +311,7 @@ class TrainEngine:
                 self.g_forward(training=True)
         ops.slerp(self.X[B:2 * B, :din], self.X[:B, :din], self.X[2 * B:, :din],
                   alpha=self._rand(inject, "alpha", None), rng=self.rng, stream=S_ALPHA)
-        self.d_forward(3 * Bp, inject, "u_drop_d", S_DROP_D, self.rowscale_loss, self.loss_d)   # + WGAN loss value
+        self.d_forward(3 * Bp, inject, "u_drop_d", S_DROP_D, self.rowscale_loss, self.loss_d, self.rowscale_d)
         # backward signals for all rows (interp rows carry the d y / d x seed)
         self.d_signals(3 * Bp, self.rowscale_d)
         nl = len(self.dhid)
@@ -355,7 +355,7 @@ class TrainEngine:
             self.g_forward(training=True)
         ops.activate_fwd(self.fake, self.tables, self.X[:B], tau=cfg.tau, u=self._rand(inject, "u_gumbel_g", None),
                          rng=self.rng, stream=S_GUMBEL_G, cond=c1)
-        self.d_forward(Bp, inject, "u_drop_g", S_DROP_G, self.rowscale_g, self.loss_g_adv)
+        self.d_forward(Bp, inject, "u_drop_g", S_DROP_G, self.rowscale_g, self.loss_g_adv, self.rowscale_g)
         self.d_signals(Bp, self.rowscale_g)
         ops.linear(self.Z[0][:Bp], self._dw(0), self.dXp, b_t=True)
         ops.activate_bwd(self.dX[:, :dd], self.X[:B, :dd], self.tables, self.dfake, tau=cfg.tau)

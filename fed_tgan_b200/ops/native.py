@@ -63,6 +63,7 @@ _rowdot_loss = _sig("ftg_rowdot_loss", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp
 _prep_select = _sig("ftg_prep_select", [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp])
 _prep_rows = _sig("ftg_prep_rows", [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _vp, _i, _vp,
                                     _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _i, _vp, _i, _i, _vp])
+_d_head = _sig("ftg_d_head", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp])
 _colsum = _sig("ftg_colsum", [_vp, _i, _i, _i, _vp, _vp, _i, _vp])
 _som = _sig("ftg_scale_outer_mask", [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp])
 _bn_fwd = _sig("ftg_bn_relu_fwd", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp])
@@ -225,6 +226,15 @@ def rowdot(a, w, bias, out, rowscale=None, loss_out=None):
     else:
         _ck(_rowdot(pa, lda, a.shape[0], a.shape[1], _p(w), _p(bias), _p(out), _stream()), "rowdot")
     return out
+
+
+def d_head(a, w, bias, y, rs_loss, loss_out, rs_sig, mask, z):
+    pa, lda = _m(a)
+    pm, ldm = _m(mask)
+    pz, ldz = _m(z)
+    _ck(_d_head(pa, lda, a.shape[0], a.shape[1], _p(w), _p(bias), _p(y), _p(rs_loss), _p(loss_out), _p(rs_sig), pm,
+                ldm, pz, ldz, _stream()), "d_head")
+    return y
 
 
 def colsum(a, out, rowscale=None, accumulate=False):

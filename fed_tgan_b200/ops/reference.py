@@ -95,6 +95,14 @@ def rowdot(a, w, bias, out, rowscale=None, loss_out=None):
     return out
 
 
+def d_head(a, w, bias, y, rs_loss, loss_out, rs_sig, mask, z):
+    """Discriminator head: ``y = a.w + b``, ``loss = sum rs_loss*y`` and the first backward signal
+    ``z = rs_sig (x) w (.) mask`` (one fused launch on the device)."""
+    rowdot(a, w, bias, y, rowscale=rs_loss, loss_out=loss_out)
+    scale_outer_mask(rs_sig, w.reshape(-1), mask, z)
+    return y
+
+
 def colsum(a, out, rowscale=None, accumulate=False):
     """``out[n] = sum_m rowscale[m] * a[m,n]``."""
     v = a.sum(0) if rowscale is None else (a * rowscale.view(-1, 1)).sum(0)

@@ -156,14 +156,18 @@ class MDGANServer:
                 samples.append(per_client)
                 pooled.append(np.concatenate(per_client))
             wd = W.continuous_similarity(samples) if samples else np.zeros((self.group.n, 0))
+            dev_w = self._device_similarity(samples)
+            if dev_w is not None:
+                wd = dev_w[1]
             if self.vgm_backend == "vb" and pooled:
                 fitted = fit_vbgmm_1d(np.stack(pooled), cfg.n_clusters, cfg.dp_prior, device=self.device)
             else:
                 fitted = [fit_sklearn_1d(p, cfg.n_clusters, cfg.dp_prior, random_state=self.seed) for p in pooled]
-            return wd, cont_ids, [f.to_array() for f in fitted]
+            return wd, cont_ids, [f.to_array() for f in fitted], dev_w
 
-        wd, cont_ids, fitted = self.group.root_compute(build)
+        wd, cont_ids, fitted, dev_w = self.group.root_compute(build)
         self.distribution_similarity_vector_continuous = wd
+        self.device_similarity = dev_w          # (JSD_norm, WD_norm, weights) from the fused kernel, or None
         agg_models, agg_comps = [], []
         it = iter(fitted)
         for ci, col in enumerate(self.meta_transformer):
@@ -178,15 +182,52 @@ class MDGANServer:
         wire = [None if m is None else m.to_array() for m in agg_models]
         self.group.call("register_transformer_information", wire, agg_comps)
 
+    def _device_similarity(self, samples):
+        """JSD / WD / final weights on the device (``ftg_stats_to_weights``): category
+        histograms and sorted GMM samples go up once, the normalised distance matrices and the
+        soft-maxed weights come back.  ``None`` when there is no GPU (numpy path is used)."""
+        dev = self.device
+        if dev is None or dev.type != "cuda":
+            return None
+        try:
+            from ..ops import native
+        except Exception:
+            return None
+        n = self.group.n
+        cv = self.category_count_vectors
+        t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).to(dev)  # noqa: E731
+        with torch.cuda.device(dev):
+            if cv:
+                hist = np.stack([np.concatenate([cv[c][i] for c in range(len(cv))]) for i in range(n)])
+                cat_off = np.concatenate([[0], np.cumsum([len(cv[c][0]) for c in range(len(cv))])])
+            else:
+                hist, cat_off = np.zeros((n, 1)), np.zeros(1)
+            if samples:
+                pool = torch.stack([torch.sort(t(np.concatenate(per), torch.float32)).values for per in samples])
+                flat = torch.cat([torch.sort(t(x, torch.float32)).values for per in samples for x in per])
+                off = np.concatenate([[0], np.cumsum([len(x) for per in samples for x in per])])
+            else:
+                pool, flat, off = None, None, np.zeros(1)
+            jsd, wd, w = native.stats_to_weights(t(hist, torch.float32), t(cat_off, torch.int32), pool, flat,
+                                                 t(off, torch.int32), t(self.rows_number_list, torch.float32))
+            return jsd.double().cpu().numpy(), wd.double().cpu().numpy(), w.double().cpu().numpy()
+
     def refit_local_transformer(self):
         # the reference walks the clients sequentially (:832-835); they are independent, so
         # the group runs them concurrently
         self.group.call("refit_transformer")
 
     def calculate_final_weights_for_aggregation(self):
-        self.weights_con_cat_combination = W.final_weights(
-            self.distribution_similarity_vector, self.distribution_similarity_vector_continuous,
-            self.rows_number_list)
+        host = W.final_weights(self.distribution_similarity_vector, self.distribution_similarity_vector_continuous,
+                               self.rows_number_list)
+        dev_w = getattr(self, "device_similarity", None)
+        if dev_w is not None:
+            # the fused kernel's result is the one used; the numpy restatement is the cross-check
+            if not np.allclose(dev_w[2], host, atol=2e-3):
+                raise RuntimeError(f"device weights {dev_w[2]} disagree with host weights {host}")
+            self.weights_con_cat_combination = dev_w[2] / dev_w[2].sum()
+        else:
+            self.weights_con_cat_combination = host
         return self.weights_con_cat_combination
 
     # ----------------------------------------------------------- sampling side

@@ -79,6 +79,10 @@ int ftg_rowdot(const float* a, int lda, int M, int K, const float* w, const floa
 /* rowdot + fused scalar  loss_out = sum_m rowscale[m] * out[m]  (WGAN loss value) */
 int ftg_rowdot_loss(const float* a, int lda, int M, int K, const float* w, const float* bias, float* out,
                     const float* rowscale, float* loss_out, ftg_stream_t stream);
+/* discriminator head: rowdot + loss value + first backward signal Z = rs_sig (x) w (.) mask, one launch */
+int ftg_d_head(const float* a, int lda, int M, int K, const float* w, const float* bias, float* y,
+               const float* rs_loss, float* loss_out, const float* rs_sig, const float* mask, int ldm, float* Z,
+               int ldz, ftg_stream_t stream);
 int ftg_colsum(const float* a, int lda, int M, int N, const float* rowscale, float* out, int accumulate,
                ftg_stream_t stream);
 int ftg_scale_outer_mask(const float* rowscale, const float* v, const float* mask, int ldm, float* out,
