@@ -182,6 +182,7 @@ def run_ours(args):
     def timed(n_rounds, e2e, tag):
         launches0 = native.launch_count()
         replay0 = client.graph_replays()
+        gen0 = getattr(server, "gen_graph_replays", 0)
         barrier()
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         start.record()
@@ -192,6 +193,7 @@ def run_ours(args):
         barrier()
         ms = start.elapsed_time(end)
         launches = (native.launch_count() - launches0) + (client.graph_replays() - replay0) * client.graph_launches()
+        launches += (getattr(server, "gen_graph_replays", 0) - gen0) * getattr(server, "gen_graph_launches", 0)
         t = torch.tensor([ms, float(launches)], dtype=torch.float64, device=dev)
         if world > 1:
             tmax = t.clone()

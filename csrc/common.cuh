@@ -16,6 +16,34 @@ extern int g_ftg_launch_count;   // defined in elementwise.cu
     if (e__ != cudaSuccess) return (int)e__;       \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------
+// Kernels of the training iteration are launched with programmatic stream serialisation: the
+// next kernel's CTAs may become resident while the current one drains, and block in
+// `griddepcontrol.wait` until the predecessor's memory is visible.  Hides launch latency and
+// prologues of the ~50 small dependent kernels of an iteration (also inside CUDA graphs).
+extern int g_ftg_pdl;            // defined in elementwise.cu; FEDTGAN_PDL=0 disables
+#define FTG_PDL_ENTER()                                        \
+  do {                                                         \
+    asm volatile("griddepcontrol.launch_dependents;");         \
+    asm volatile("griddepcontrol.wait;" ::: "memory");         \
+  } while (0)
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t ftg_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_ftg_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline int ftg_cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 // ---------------------------------------------------------------- Philox4x32-10

@@ -2,17 +2,24 @@
 // Each kernel's fp32 PyTorch oracle is the function of the same name (without the ftg_
 // prefix) in fed_tgan_b200/ops/reference.py.
 #include "common.cuh"
+#include <cstdlib>
 
 int g_ftg_launch_count = 0;
+int g_ftg_pdl = [] {
+  const char* e = getenv("FEDTGAN_PDL");
+  return (e && e[0] == '0') ? 0 : 1;
+}();
+extern "C" void ftg_set_pdl(int on) { g_ftg_pdl = on ? 1 : 0; }
 
 extern "C" const char* ftg_version(void) { return "fedtgan_b200 0.1.0 (sm_100a)"; }
 extern "C" int ftg_last_launch_count(void) { return g_ftg_launch_count; }
 
 // ------------------------------------------------------------------ rng tick
-__global__ void k_tick(int64_t* state) { state[1] += 1; }
+__global__ void k_tick(int64_t* state) {
+  FTG_PDL_ENTER(); state[1] += 1; }
 
 extern "C" int ftg_tick(int64_t* rng_state, ftg_stream_t stream) {
-  k_tick<<<1, 1, 0, (cudaStream_t)stream>>>(rng_state);
+  ftg_launch(k_tick, dim3(1), dim3(1), 0, (cudaStream_t)stream, rng_state);
   FTG_LAUNCH_CHECK();
   return 0;
 }
@@ -227,6 +234,7 @@ __global__ void __launch_bounds__(1024) k_d_head(const float* __restrict__ a, in
                                                  const float* __restrict__ rs_loss, float* loss_out,
                                                  const float* __restrict__ rs_sig, const float* __restrict__ mask,
                                                  int ldm, float* Z, int ldz) {
+  FTG_PDL_ENTER();
   if (blockIdx.x == 0) {
     __shared__ float red[32];
     const int sub = threadIdx.x & 7, rloc = threadIdx.x >> 3, rpp = blockDim.x >> 3;
@@ -265,7 +273,7 @@ extern "C" int ftg_d_head(const float* a, int lda, int M, int K, const float* w,
                           float* Z, int ldz, ftg_stream_t stream) {
   int extra = ftg_cdiv((long long)M * K, 1024 * 4);
   if (extra < 1) extra = 1;
-  k_d_head<<<1 + extra, 1024, 0, (cudaStream_t)stream>>>(a, lda, M, K, w, bias, y, rs_loss, loss_out, rs_sig, mask, ldm,
+  ftg_launch(k_d_head, dim3(1 + extra), dim3(1024), 0, (cudaStream_t)stream, a, lda, M, K, w, bias, y, rs_loss, loss_out, rs_sig, mask, ldm,
                                                         Z, ldz);
   FTG_LAUNCH_CHECK();
   return 0;
@@ -282,6 +290,7 @@ extern "C" int ftg_rowdot_loss(const float* a, int lda, int M, int K, const floa
 // blockDim = (32, 32): 32 columns per block, rows strided over y; deterministic tree.
 __global__ void __launch_bounds__(1024) k_colsum(const float* __restrict__ a, int lda, int M, int N,
                                                  const float* __restrict__ rowscale, float* out, int accumulate) {
+  FTG_PDL_ENTER();
   __shared__ float part[32][33];
   int n = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
@@ -299,7 +308,7 @@ __global__ void __launch_bounds__(1024) k_colsum(const float* __restrict__ a, in
 
 extern "C" int ftg_colsum(const float* a, int lda, int M, int N, const float* rowscale, float* out, int accumulate,
                           ftg_stream_t stream) {
-  k_colsum<<<ftg_cdiv(N, 32), dim3(32, 32), 0, (cudaStream_t)stream>>>(a, lda, M, N, rowscale, out, accumulate);
+  ftg_launch(k_colsum, dim3(ftg_cdiv(N, 32)), dim3(dim3(32, 32)), 0, (cudaStream_t)stream, a, lda, M, N, rowscale, out, accumulate);
   FTG_LAUNCH_CHECK();
   return 0;
 }
@@ -341,6 +350,7 @@ __global__ void __launch_bounds__(BN_F * BN_R)
 k_bn_relu_fwd(const float* __restrict__ a, int lda, int B, int H, const float* __restrict__ gamma,
               const float* __restrict__ beta, float* running_mean, float* running_var, float* out, int ldo,
               float* save_mean, float* save_invstd, float eps, float momentum, float* nbt) {
+  FTG_PDL_ENTER();
   __shared__ float red[BN_R / 4][BN_F];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int h = blockIdx.x * BN_F + tx;
@@ -405,8 +415,7 @@ extern "C" int ftg_bn_relu_fwd(const float* a, int lda, int B, int H, const floa
                                float* save_invstd, int training, float eps, float momentum,
                                float* num_batches_tracked, ftg_stream_t stream) {
   if (training) {
-    k_bn_relu_fwd<<<ftg_cdiv(H, BN_F), dim3(BN_F, BN_R), 0, (cudaStream_t)stream>>>(
-        a, lda, B, H, gamma, beta, running_mean, running_var, out, ldo, save_mean, save_invstd, eps, momentum,
+    ftg_launch(k_bn_relu_fwd, dim3(ftg_cdiv(H, BN_F)), dim3(dim3(BN_F, BN_R)), 0, (cudaStream_t)stream, a, lda, B, H, gamma, beta, running_mean, running_var, out, ldo, save_mean, save_invstd, eps, momentum,
         num_batches_tracked);
   } else {
     k_bn_relu_eval<<<dim3(ftg_cdiv(H, 32), ftg_cdiv(B, 128)), dim3(32, 8), 0, (cudaStream_t)stream>>>(
@@ -424,6 +433,7 @@ k_bn_relu_bwd(const float* __restrict__ dout, int lddo, const float* __restrict_
               const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
               const float* __restrict__ gamma, const float* __restrict__ beta, float* da, int ldda, float* dgamma,
               float* dbeta, float* dbias_fc) {
+  FTG_PDL_ENTER();
   __shared__ float red[BN_R / 4][BN_F];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int h = blockIdx.x * BN_F + tx;
@@ -479,8 +489,7 @@ extern "C" int ftg_bn_relu_bwd(const float* dout, int lddo, const float* a, int 
                                const float* save_mean, const float* save_invstd, const float* gamma,
                                const float* beta, float* da, int ldda, float* dgamma, float* dbeta,
                                ftg_stream_t stream) {
-  k_bn_relu_bwd<<<ftg_cdiv(H, BN_F), dim3(BN_F, BN_R), 0, (cudaStream_t)stream>>>(
-      dout, lddo, a, lda, B, H, save_mean, save_invstd, gamma, beta, da, ldda, dgamma, dbeta, nullptr);
+  ftg_launch(k_bn_relu_bwd, dim3(ftg_cdiv(H, BN_F)), dim3(dim3(BN_F, BN_R)), 0, (cudaStream_t)stream, dout, lddo, a, lda, B, H, save_mean, save_invstd, gamma, beta, da, ldda, dgamma, dbeta, nullptr);
   FTG_LAUNCH_CHECK();
   return 0;
 }
@@ -489,8 +498,7 @@ extern "C" int ftg_bn_relu_bwd_bias(const float* dout, int lddo, const float* a,
                                     const float* save_mean, const float* save_invstd, const float* gamma,
                                     const float* beta, float* da, int ldda, float* dgamma, float* dbeta,
                                     float* dbias_fc, ftg_stream_t stream) {
-  k_bn_relu_bwd<<<ftg_cdiv(H, BN_F), dim3(BN_F, BN_R), 0, (cudaStream_t)stream>>>(
-      dout, lddo, a, lda, B, H, save_mean, save_invstd, gamma, beta, da, ldda, dgamma, dbeta, dbias_fc);
+  ftg_launch(k_bn_relu_bwd, dim3(ftg_cdiv(H, BN_F)), dim3(dim3(BN_F, BN_R)), 0, (cudaStream_t)stream, dout, lddo, a, lda, B, H, save_mean, save_invstd, gamma, beta, da, ldda, dgamma, dbeta, dbias_fc);
   FTG_LAUNCH_CHECK();
   return 0;
 }
@@ -505,6 +513,7 @@ k_activate_fwd(const float* __restrict__ fake, int ldf, int dd, int n_spans, con
                const int* __restrict__ span_width, const int* __restrict__ span_kind,
                const int* __restrict__ col_span, float* out, int ldo, float inv_tau, const float* u, int ldu,
                const int64_t* state, int stream_id, const float* cond, int ldc, int n_opt, int use_noise) {
+  FTG_PDL_ENTER();
   extern __shared__ float sm[];
   float* val = sm;                 // [dd]
   float* smax = sm + dd;           // [n_spans]
@@ -553,7 +562,7 @@ extern "C" int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n
                                 ftg_stream_t stream) {
   size_t smem = (size_t)(dd + 2 * n_spans) * sizeof(float);
   if (smem > 48 * 1024) return FTG_ERR_UNSUPPORTED;
-  k_activate_fwd<<<B, 128, smem, (cudaStream_t)stream>>>(fake, ldf, dd, n_spans, span_start, span_width, span_kind,
+  ftg_launch(k_activate_fwd, dim3(B), dim3(128), smem, (cudaStream_t)stream, fake, ldf, dd, n_spans, span_start, span_width, span_kind,
                                                          col_span, out, ldo, 1.f / tau, u, ldu, rng_state, rng_stream,
                                                          cond, ldc, n_opt, use_noise);
   FTG_LAUNCH_CHECK();
@@ -564,6 +573,7 @@ extern "C" int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n
 __global__ void k_activate_bwd(const float* __restrict__ dout, int lddo, const float* __restrict__ act, int lda, int B,
                                int n_spans, const int* __restrict__ span_start, const int* __restrict__ span_width,
                                const int* __restrict__ span_kind, float* dfake, int ldf, float inv_tau, int accumulate) {
+  FTG_PDL_ENTER();
   long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (long long)B * n_spans) return;
   int row = (int)(t / n_spans), s = (int)(t % n_spans);
@@ -590,7 +600,7 @@ extern "C" int ftg_activate_bwd(const float* dout, int lddo, const float* act, i
                                 const int* span_start, const int* span_width, const int* span_kind, float* dfake,
                                 int ldf, float tau, int accumulate, ftg_stream_t stream) {
   long long n_work = (long long)B * n_spans;
-  k_activate_bwd<<<ftg_cdiv(n_work, 128), 128, 0, (cudaStream_t)stream>>>(dout, lddo, act, lda, B, n_spans, span_start,
+  ftg_launch(k_activate_bwd, dim3(ftg_cdiv(n_work, 128)), dim3(128), 0, (cudaStream_t)stream, dout, lddo, act, lda, B, n_spans, span_start,
                                                                           span_width, span_kind, dfake, ldf, 1.f / tau,
                                                                           accumulate);
   FTG_LAUNCH_CHECK();
@@ -607,6 +617,7 @@ __global__ void k_cond_loss(const float* __restrict__ fake, int ldf, const float
                             const float* __restrict__ mask, int ldm, int B, int n_col,
                             const int* __restrict__ soft_start, const int* __restrict__ soft_width,
                             const int* __restrict__ soft_cstart, float* dfake, int lddf, float* loss_out) {
+  FTG_PDL_ENTER();
   __shared__ float red[32];
   long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   float contrib = 0.f;
@@ -648,7 +659,7 @@ extern "C" int ftg_cond_loss(const float* fake, int ldf, const float* cond, int 
     ++g_ftg_launch_count;
   }
   long long n_work = (long long)B * n_col;
-  k_cond_loss<<<ftg_cdiv(n_work, 128), 128, 0, s>>>(fake, ldf, cond, ldc, mask, ldm, B, n_col, soft_start, soft_width,
+  ftg_launch(k_cond_loss, dim3(ftg_cdiv(n_work, 128)), dim3(128), 0, s, fake, ldf, cond, ldc, mask, ldm, B, n_col, soft_start, soft_width,
                                                     soft_cstart, dfake, lddf, loss_out);
   FTG_LAUNCH_CHECK();
   return 0;
@@ -658,6 +669,7 @@ extern "C" int ftg_cond_loss(const float* fake, int ldf, const float* cond, int 
 // One warp per row.
 __global__ void k_slerp(const float* __restrict__ low, int ldl, const float* __restrict__ high, int ldh, float* out,
                         int ldo, int B, int din, const float* alpha, const int64_t* state, int stream_id) {
+  FTG_PDL_ENTER();
   int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   int lane = threadIdx.x & 31;
   if (row >= B) return;
@@ -680,7 +692,7 @@ __global__ void k_slerp(const float* __restrict__ low, int ldl, const float* __r
 
 extern "C" int ftg_slerp(const float* low, int ldl, const float* high, int ldh, float* out, int ldo, int B, int din,
                          const float* alpha, const int64_t* rng_state, int rng_stream, ftg_stream_t stream) {
-  k_slerp<<<ftg_cdiv(B, 4), 128, 0, (cudaStream_t)stream>>>(low, ldl, high, ldh, out, ldo, B, din, alpha, rng_state,
+  ftg_launch(k_slerp, dim3(ftg_cdiv(B, 4)), dim3(128), 0, (cudaStream_t)stream, low, ldl, high, ldh, out, ldo, B, din, alpha, rng_state,
                                                             rng_stream);
   FTG_LAUNCH_CHECK();
   return 0;
@@ -689,6 +701,7 @@ extern "C" int ftg_slerp(const float* low, int ldl, const float* high, int ldh, 
 // ---------------------------------------------------------------- gp_penalty
 // One CTA per pack row: ||g||, penalty contribution, and in-place d pen / d g.
 __global__ void k_gp_penalty(float* g, int ldg, int Bp, int Din, float* pen_out, float lambda_) {
+  FTG_PDL_ENTER();
   __shared__ float red[32];
   float* row = g + (size_t)blockIdx.x * ldg;
   float s = 0.f;
@@ -706,7 +719,7 @@ extern "C" int ftg_gp_penalty(float* g, int ldg, int Bp, int Din, float* pen_out
   cudaStream_t s = (cudaStream_t)stream;
   cudaError_t e = cudaMemsetAsync(pen_out, 0, sizeof(float), s);
   if (e != cudaSuccess) return (int)e;
-  k_gp_penalty<<<Bp, 256, 0, s>>>(g, ldg, Bp, Din, pen_out, lambda_);
+  ftg_launch(k_gp_penalty, dim3(Bp), dim3(256), 0, s, g, ldg, Bp, Din, pen_out, lambda_);
   FTG_LAUNCH_CHECK();
   return 0;
 }
@@ -715,6 +728,7 @@ extern "C" int ftg_gp_penalty(float* g, int ldg, int Bp, int Din, float* pen_out
 __global__ void k_adam(float* __restrict__ param, const float* __restrict__ grad, float* __restrict__ m,
                        float* __restrict__ v, long long n, const int64_t* state, float lr, float b1, float b2,
                        float eps, float wd) {
+  FTG_PDL_ENTER();
   float t = (float)state[1];
   float bc1 = 1.f - powf(b1, t), bc2 = 1.f - powf(b2, t);
   float step = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
@@ -749,7 +763,7 @@ extern "C" int ftg_adam(float* param, const float* grad, float* exp_avg, float* 
                         const int64_t* rng_state, float lr, float beta1, float beta2, float eps, float weight_decay,
                         ftg_stream_t stream) {
   if (n <= 0) return 0;
-  k_adam<<<ftg_cdiv((n + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, rng_state,
+  ftg_launch(k_adam, dim3(ftg_cdiv((n + 3) / 4, 256)), dim3(256), 0, (cudaStream_t)stream, param, grad, exp_avg, exp_avg_sq, n, rng_state,
                                                                        lr, beta1, beta2, eps, weight_decay);
   FTG_LAUNCH_CHECK();
   return 0;

@@ -205,6 +205,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   const int nkb = (p.K + BK - 1) / BK;
   const int kb0 = (int)((long long)z * nkb / split_k), kb1 = (int)((long long)(z + 1) * nkb / split_k);
 
+  // PDL: let the next kernel become resident now; our own prologue (barrier init, TMEM
+  // allocation, descriptor prefetch) overlaps the predecessor's tail, then we wait for its data.
+  asm volatile("griddepcontrol.launch_dependents;");
   if (threadIdx.x == 0) {
     TL(0);
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
@@ -215,15 +218,18 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  asm volatile("griddepcontrol.wait;" ::: "memory");        // predecessor's outputs are visible from here on
 
   if (warp == 0 && lane == 0) {
     // ------------------------------------------------------------ TMA producer
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
     int s = 0;
     uint32_t phase = 0;
     TL(1);
@@ -371,10 +377,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         const int j = t >> log2S, q = t & (S - 1);
         const int f = r * cpr + j * 128 + et;
         const uint32_t local = stage_u32 + (uint32_t)(((f >> 4) * SLD + (f & 15) * 4) * 4);
-        uint32_t remote;
-        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(q));
-        asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
-                     : "=f"(v[t].x), "=f"(v[t].y), "=f"(v[t].z), "=f"(v[t].w) : "r"(remote) : "memory");
+        v[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m0 + (f >> 4) < p.M) {                           // rows past M carry nothing: skip their DSMEM traffic
+          uint32_t remote;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(q));
+          asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(v[t].x), "=f"(v[t].y), "=f"(v[t].z), "=f"(v[t].w) : "r"(remote) : "memory");
+        }
       }
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -451,23 +460,28 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
   ++g_ftg_launch_count;
-  if (!cluster_mode) {
-    k_gemm_tc<A_MN, B_MN, EPI><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ma, mb, p, split_k, ws, ctr, vec_ok, 0);
-    return (int)cudaPeekAtLastError();
-  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 1;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = (unsigned)split_k;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (cluster_mode) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 1;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = (unsigned)split_k;
+    ++na;
+  }
+  if (g_ftg_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI>, ma, mb, p, split_k, ws, ctr, vec_ok, 1);
+  cfg.numAttrs = na;
+  return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI>, ma, mb, p, split_k, ws, ctr, vec_ok, cluster_mode);
 }
 
 template <bool A_MN, bool B_MN>

@@ -33,6 +33,7 @@ k_prep_select(const float* __restrict__ cum_p, int n_col, int max_w, const int* 
               const int* __restrict__ soft_cstart, const int* __restrict__ row_ptr, const int* __restrict__ row_ids,
               int* col, int* opt, int* perm, int* rid, int B, int P2, const int64_t* state, int s_col, int s_perm,
               int s_row) {
+  FTG_PDL_ENTER();
   extern __shared__ unsigned char smem_raw[];
   float* key = reinterpret_cast<float*>(smem_raw);
   int* idx = reinterpret_cast<int*>(key + P2);
@@ -89,6 +90,7 @@ struct PrepRows {
 };
 
 __global__ void __launch_bounds__(128) k_prep_rows(const PrepRows P) {
+  FTG_PDL_ENTER();
   __shared__ int s_c, s_o;
   const int i = blockIdx.x;
   if (threadIdx.x == 0) {
@@ -146,7 +148,7 @@ extern "C" int ftg_prep_select(const float* cum_p, int n_col, int max_w, const i
   while (P2 < B) P2 <<= 1;
   if (P2 > 4096) return FTG_ERR_UNSUPPORTED;
   int threads = P2 < 1024 ? (P2 < 32 ? 32 : P2) : 1024;
-  k_prep_select<<<1, threads, (size_t)P2 * 12, (cudaStream_t)stream>>>(cum_p, n_col, max_w, soft_width, soft_cstart,
+  ftg_launch(k_prep_select, dim3(1), dim3(threads), (size_t)P2 * 12, (cudaStream_t)stream, cum_p, n_col, max_w, soft_width, soft_cstart,
                                                                       row_ptr, row_ids, col, opt, perm, rid, B, P2,
                                                                       rng_state, s_col, s_perm, s_row);
   FTG_LAUNCH_CHECK();
@@ -165,7 +167,7 @@ extern "C" int ftg_prep_rows(int mode, int* col, int* opt, const int* perm, cons
   P.m_out = m_out; P.ldm = ldm; P.n_col = n_col; P.vals = vals; P.n_tanh = n_tanh; P.codes = codes;
   P.tanh_start = tanh_start; P.soft_start = soft_start; P.real_out = real_out; P.ldr = ldr; P.dd = dd;
   P.cum_p = cum_p; P.max_w = max_w; P.soft_width = soft_width; P.state = rng_state; P.s_z = s_z; P.s_col = s_col;
-  k_prep_rows<<<B, 128, 0, (cudaStream_t)stream>>>(P);
+  ftg_launch(k_prep_rows, dim3(B), dim3(128), 0, (cudaStream_t)stream, P);
   FTG_LAUNCH_CHECK();
   return 0;
 }

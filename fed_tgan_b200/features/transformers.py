@@ -186,6 +186,37 @@ class BGM_CTGAN_Transformer(Transformer):
         val = np.clip((col - mu) / (4.0 * sd), -0.99, 0.99)
         return val, sel
 
+    def transform_compact_device(self, data, device):
+        """Same as ``transform_compact`` but the continuous columns are encoded by the
+        ``vgm_encode`` kernel (posterior over active modes, Philox mode draw, normalised scalar)
+        writing straight into the compact table on ``device``; returns device tensors."""
+        import torch
+
+        from .. import ops
+
+        data = np.asarray(data, dtype=np.float64)
+        n = len(data)
+        lay = self.layout
+        dev = torch.device(device)
+        vals = torch.zeros(n, max(lay.n_tanh, 1), dtype=torch.float32, device=dev)[:, : lay.n_tanh]
+        codes = torch.zeros(n, lay.n_col, dtype=torch.int32, device=dev)
+        rng = ops.RngState(int(self.rng.integers(1 << 30)), dev)
+        rng.tick()
+        t = s = 0
+        f32 = lambda a: torch.as_tensor(np.ascontiguousarray(a), dtype=torch.float32).to(dev)  # noqa: E731
+        for j, info in enumerate(self.meta):
+            if info["type"] == CONTINUOUS:
+                gm, mask = self.model[j], self.components[j]
+                ops.vgm_encode(f32(data[:, j]), f32(gm.logit_const()), f32(gm.means), f32(gm.covs),
+                               torch.as_tensor(np.asarray(mask, dtype=bool)).to(dev), None, vals[:, t], codes[:, s],
+                               rng=rng, stream=j)
+                t += 1
+                s += 1
+            else:
+                codes[:, s] = torch.as_tensor(_onehot_by_lookup(data[:, j], info["i2s"]).astype(np.int32)).to(dev)
+                s += 1
+        return vals, codes
+
     def transform_compact(self, data):
         """``(vals [rows, n_tanh] float32, codes [rows, n_col] int32)``."""
         data = np.asarray(data, dtype=np.float64)

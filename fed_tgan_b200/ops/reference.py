@@ -375,10 +375,12 @@ def vgm_decode(act, tables, mu, sd, cat_ids, cat_off, col_is_cont, out):
     return out
 
 
-def vgm_encode(x, logit_const, mu, var, active, u, val_out, code_out):
+def vgm_encode(x, logit_const, mu, var, active, u, val_out, code_out, rng=None, stream=0):
     """One continuous column: posterior over active modes, sampled mode, normalised scalar.
 
     ``logit_const, mu, var`` are ``[K]``; ``active`` a bool ``[K]`` mask; ``u`` uniforms."""
+    if u is None:
+        u = rng.uniform(x.shape[0])
     lc, m, v = logit_const[active], mu[active], var[active]
     logit = lc.view(1, -1) - 0.5 * (x.view(-1, 1) - m.view(1, -1)) ** 2 / v.view(1, -1)
     p = torch.softmax(logit, dim=1) + 1e-6

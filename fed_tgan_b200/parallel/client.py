@@ -141,7 +141,11 @@ class MDGANClient:
         optimiser state (reference ``:295-317``)."""
         self.transformer.refit(self.train, self.meta_file, self.label_encoder, self.cat_cols, self.ord_cols,
                                self.model, self.components)
-        vals, codes = self.transformer.transform_compact(self.train)
+        if self.device.type == "cuda" and self.vgm_backend == "vb":
+            dv, dc = self.transformer.transform_compact_device(self.train, self.device)     # K12 on the device
+            vals, codes = dv.cpu().numpy(), dc.cpu().numpy()
+        else:
+            vals, codes = self.transformer.transform_compact(self.train)
         self.out_info = self.transformer.output_info
         self.data_dim = self.transformer.output_dim
         self.layout = self.transformer.layout

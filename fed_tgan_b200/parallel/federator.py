@@ -303,9 +303,12 @@ class MDGANServer:
                 gen.generate(self._snap, self.cfg.sample_rows, out=self._slots[0]["dev"])      # warm-up, uncaptured
                 self._gen_stream.synchronize()
                 self._gen_graph = torch.cuda.CUDAGraph()
+                n0 = native.launch_count()
                 with torch.cuda.graph(self._gen_graph, stream=self._gen_stream):
                     gen.generate(self._snap, self.cfg.sample_rows, out=self._gen_out())
+                self.gen_graph_launches = native.launch_count() - n0
             self._gen_graph.replay()
+            self.gen_graph_replays = getattr(self, "gen_graph_replays", 0) + 1
             slot["dev"].copy_(self._gen_out(), non_blocking=True)
             slot["host"].copy_(slot["dev"], non_blocking=True)
             slot["done"].record(self._gen_stream)

@@ -87,3 +87,27 @@ def test_local_federation_on_device(tmp_path):
     df = pd.read_csv(tmp_path / "Adult_result" / "Adult_synthesis_epoch_1.csv")
     assert len(df) == 2000 and list(df.columns) == schema.columns
     assert np.isfinite(df[schema.continuous].to_numpy()).all()
+
+
+def test_device_vgm_encode_matches_host_distribution():
+    from fed_tgan_b200.features.transformers import BGM_CTGAN_Transformer
+
+    rng = np.random.default_rng(0)
+    n = 6000
+    data = np.stack([np.concatenate([rng.normal(0, 1, n // 2), rng.normal(9, 0.7, n // 2)]),
+                     rng.integers(0, 5, n).astype(float), rng.exponential(2, n)], 1)
+    t = BGM_CTGAN_Transformer(backend="vb", seed=0)
+    t.fit(data, (1,))
+    hv, hc = t.transform_compact(data)
+    dv, dc = t.transform_compact_device(data, "cuda:0")
+    dv, dc = dv.cpu().numpy(), dc.cpu().numpy()
+    assert dv.shape == hv.shape and dc.shape == hc.shape
+    assert np.array_equal(dc[:, 1], hc[:, 1])                         # categorical codes are deterministic
+    for col in (0, 2):                                                # mode frequencies agree statistically
+        k = int(max(hc[:, col].max(), dc[:, col].max())) + 1
+        fh = np.bincount(hc[:, col], minlength=k) / n
+        fd = np.bincount(dc[:, col], minlength=k) / n
+        assert np.abs(fh - fd).max() < 0.03
+    rt = t.inverse_transform(t.expand(dv, dc))
+    inside = np.abs(dv).max(axis=1) < 0.99
+    assert np.abs(rt[inside][:, [0, 2]] - data[inside][:, [0, 2]]).max() < 1e-2
