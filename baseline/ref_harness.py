@@ -67,8 +67,9 @@ def _spawn(spec, gpu, log):
     env = dict(os.environ)
     env["CUDA_VISIBLE_DEVICES"] = "" if gpu is None else str(gpu)
     env["PYTHONPATH"] = ""
+    # torchrun exports OMP_NUM_THREADS=1; the reference is CPU heavy, so give it the default threading back
     for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "GROUP_RANK", "LOCAL_WORLD_SIZE",
-              "TORCHELASTIC_RUN_ID"):
+              "TORCHELASTIC_RUN_ID", "OMP_NUM_THREADS"):
         env.pop(k, None)
     fh = open(log, "w")
     return subprocess.Popen([sys.executable, os.path.join(HERE, "ref_worker.py"), json.dumps(spec)],

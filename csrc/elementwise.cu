@@ -512,12 +512,15 @@ __global__ void __launch_bounds__(128)
 k_activate_fwd(const float* __restrict__ fake, int ldf, int dd, int n_spans, const int* __restrict__ span_start,
                const int* __restrict__ span_width, const int* __restrict__ span_kind,
                const int* __restrict__ col_span, float* out, int ldo, float inv_tau, const float* u, int ldu,
-               const int64_t* state, int stream_id, const float* cond, int ldc, int n_opt, int use_noise) {
+               const int64_t* state, int stream_id, const float* cond, int ldc, int n_opt, int use_noise,
+               const float* __restrict__ real, int ldr, float* interp, int ldi, const float* alpha, int alpha_stream) {
   FTG_PDL_ENTER();
   extern __shared__ float sm[];
+  __shared__ float red[32];
   float* val = sm;                 // [dd]
   float* smax = sm + dd;           // [n_spans]
   float* sinv = smax + n_spans;    // [n_spans]
+  float* rowbuf = sinv + n_spans;  // [dd + n_opt]  the finished fake_cat row (only used with slerp)
   const int row = blockIdx.x;
   const float* x = fake + (size_t)row * ldf;
   float* o = out + (size_t)row * ldo;
@@ -549,10 +552,49 @@ k_activate_fwd(const float* __restrict__ fake, int ldf, int dd, int n_spans, con
   __syncthreads();
   for (int j = threadIdx.x; j < dd; j += blockDim.x) {
     const int s = col_span[j];
-    o[j] = (span_kind[s] == 0) ? val[j] : expf(val[j] - smax[s]) * sinv[s];
+    const float v = (span_kind[s] == 0) ? val[j] : expf(val[j] - smax[s]) * sinv[s];
+    o[j] = v;
+    if (interp) rowbuf[j] = v;
   }
   if (cond)
-    for (int j = threadIdx.x; j < n_opt; j += blockDim.x) o[dd + j] = cond[(size_t)row * ldc + j];
+    for (int j = threadIdx.x; j < n_opt; j += blockDim.x) {
+      const float c = cond[(size_t)row * ldc + j];
+      o[dd + j] = c;
+      if (interp) rowbuf[dd + j] = c;
+    }
+  if (!interp) return;
+  // fused slerp (ctgan.py:231-237): interp = slerp(alpha, low = real_cat row, high = this fake_cat row)
+  __syncthreads();
+  const int din = dd + n_opt;
+  const float* l = real + (size_t)row * ldr;
+  float ll = 0.f, hh = 0.f, lh = 0.f;
+  for (int j = threadIdx.x; j < din; j += blockDim.x) {
+    const float a = l[j], b = rowbuf[j];
+    ll += a * a; hh += b * b; lh += a * b;
+  }
+  ll = block_sum(ll, red);
+  hh = block_sum(hh, red);
+  lh = block_sum(lh, red);
+  const float omega = acosf(lh / (sqrtf(ll) * sqrtf(hh)));
+  const float so = sinf(omega);
+  const float a = alpha ? alpha[row] : philox_uniform(state, alpha_stream, (uint32_t)row);
+  const float wl = sinf((1.f - a) * omega) / so, wh = sinf(a * omega) / so;
+  float* io = interp + (size_t)row * ldi;
+  for (int j = threadIdx.x; j < din; j += blockDim.x) io[j] = wl * l[j] + wh * rowbuf[j];
+}
+
+static int activate_fwd_launch(const float* fake, int ldf, int B, int dd, int n_spans, const int* span_start,
+                               const int* span_width, const int* span_kind, const int* col_span, float* out, int ldo,
+                               float tau, const float* u, int ldu, const int64_t* rng_state, int rng_stream,
+                               const float* cond, int ldc, int n_opt, int use_noise, const float* real, int ldr,
+                               float* interp, int ldi, const float* alpha, int alpha_stream, ftg_stream_t stream) {
+  size_t smem = (size_t)(dd + 2 * n_spans + (interp ? dd + n_opt : 0)) * sizeof(float);
+  if (smem > 48 * 1024) return FTG_ERR_UNSUPPORTED;
+  ftg_launch(k_activate_fwd, dim3(B), dim3(128), smem, (cudaStream_t)stream, fake, ldf, dd, n_spans, span_start,
+             span_width, span_kind, col_span, out, ldo, 1.f / tau, u, ldu, rng_state, rng_stream, cond, ldc, n_opt,
+             use_noise, real, ldr, interp, ldi, alpha, alpha_stream);
+  FTG_LAUNCH_CHECK();
+  return 0;
 }
 
 extern "C" int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n_spans, const int* span_start,
@@ -560,39 +602,82 @@ extern "C" int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n
                                 int ldo, float tau, const float* u, int ldu, const int64_t* rng_state,
                                 int rng_stream, const float* cond, int ldc, int n_opt, int use_noise,
                                 ftg_stream_t stream) {
-  size_t smem = (size_t)(dd + 2 * n_spans) * sizeof(float);
-  if (smem > 48 * 1024) return FTG_ERR_UNSUPPORTED;
-  ftg_launch(k_activate_fwd, dim3(B), dim3(128), smem, (cudaStream_t)stream, fake, ldf, dd, n_spans, span_start, span_width, span_kind,
-                                                         col_span, out, ldo, 1.f / tau, u, ldu, rng_state, rng_stream,
-                                                         cond, ldc, n_opt, use_noise);
-  FTG_LAUNCH_CHECK();
-  return 0;
+  return activate_fwd_launch(fake, ldf, B, dd, n_spans, span_start, span_width, span_kind, col_span, out, ldo, tau, u,
+                             ldu, rng_state, rng_stream, cond, ldc, n_opt, use_noise, nullptr, 0, nullptr, 0, nullptr,
+                             0, stream);
+}
+
+// activate + concat + slerp in one launch: also writes interp = slerp(alpha, real, out) row by row
+extern "C" int ftg_activate_fwd_slerp(const float* fake, int ldf, int B, int dd, int n_spans, const int* span_start,
+                                      const int* span_width, const int* span_kind, const int* col_span, float* out,
+                                      int ldo, float tau, const float* u, int ldu, const int64_t* rng_state,
+                                      int rng_stream, const float* cond, int ldc, int n_opt, int use_noise,
+                                      const float* real, int ldr, float* interp, int ldi, const float* alpha,
+                                      int alpha_stream, ftg_stream_t stream) {
+  return activate_fwd_launch(fake, ldf, B, dd, n_spans, span_start, span_width, span_kind, col_span, out, ldo, tau, u,
+                             ldu, rng_state, rng_stream, cond, ldc, n_opt, use_noise, real, ldr, interp, ldi, alpha,
+                             alpha_stream, stream);
 }
 
 // -------------------------------------------------------------- activate_bwd
+// Optionally fused with cond_loss (ctgan.py:174-194): the thread that owns (row, softmax span j)
+// also adds m[row,j]/B * (softmax(fake span) - onehot(target)) and the span's CE to the loss.
 __global__ void k_activate_bwd(const float* __restrict__ dout, int lddo, const float* __restrict__ act, int lda, int B,
                                int n_spans, const int* __restrict__ span_start, const int* __restrict__ span_width,
-                               const int* __restrict__ span_kind, float* dfake, int ldf, float inv_tau, int accumulate) {
+                               const int* __restrict__ span_kind, float* dfake, int ldf, float inv_tau, int accumulate,
+                               const float* __restrict__ fake, int ldfk, const float* __restrict__ cond, int ldc,
+                               const float* __restrict__ mask, int ldm, const int* __restrict__ col_soft,
+                               const int* __restrict__ soft_cstart, float* loss_out) {
   FTG_PDL_ENTER();
+  __shared__ float red[32];
   long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= (long long)B * n_spans) return;
-  int row = (int)(t / n_spans), s = (int)(t % n_spans);
-  int st = span_start[s], w = span_width[s];
-  const float* d = dout + (size_t)row * lddo + st;
-  const float* y = act + (size_t)row * lda + st;
-  float* o = dfake + (size_t)row * ldf + st;
-  if (span_kind[s] == 0) {
-    for (int j = 0; j < w; ++j) {
-      float g = d[j] * (1.f - y[j] * y[j]);
-      o[j] = accumulate ? o[j] + g : g;
+  float contrib = 0.f;
+  if (t < (long long)B * n_spans) {
+    int row = (int)(t / n_spans), s = (int)(t % n_spans);
+    int st = span_start[s], w = span_width[s];
+    const float* d = dout + (size_t)row * lddo + st;
+    const float* y = act + (size_t)row * lda + st;
+    float* o = dfake + (size_t)row * ldf + st;
+    if (span_kind[s] == 0) {
+      for (int j = 0; j < w; ++j) {
+        float g = d[j] * (1.f - y[j] * y[j]);
+        o[j] = accumulate ? o[j] + g : g;
+      }
+    } else {
+      float dot = 0.f;
+      for (int j = 0; j < w; ++j) dot += d[j] * y[j];
+      float mj = 0.f;
+      int target = 0;
+      float lse = 0.f;
+      const float* x = nullptr;
+      if (loss_out) {
+        const int js = col_soft[st];
+        mj = mask[(size_t)row * ldm + js];
+        if (mj != 0.f) {
+          x = fake + (size_t)row * ldfk + st;
+          const float* c = cond + (size_t)row * ldc + soft_cstart[js];
+          float best = c[0], mx = x[0];
+          for (int k = 1; k < w; ++k) {
+            if (c[k] > best) { best = c[k]; target = k; }
+            mx = fmaxf(mx, x[k]);
+          }
+          float sum = 0.f;
+          for (int k = 0; k < w; ++k) sum += expf(x[k] - mx);
+          lse = mx + logf(sum);
+          contrib = (lse - x[target]) * mj;
+        }
+      }
+      const float scale = mj / (float)B;
+      for (int j = 0; j < w; ++j) {
+        float g = y[j] * (d[j] - dot) * inv_tau;
+        if (mj != 0.f) g += scale * (expf(x[j] - lse) - (j == target ? 1.f : 0.f));
+        o[j] = accumulate ? o[j] + g : g;
+      }
     }
-  } else {
-    float dot = 0.f;
-    for (int j = 0; j < w; ++j) dot += d[j] * y[j];
-    for (int j = 0; j < w; ++j) {
-      float g = y[j] * (d[j] - dot) * inv_tau;
-      o[j] = accumulate ? o[j] + g : g;
-    }
+  }
+  if (loss_out) {
+    float tot = block_sum(contrib, red);
+    if (threadIdx.x == 0 && tot != 0.f) atomicAdd(loss_out, tot / (float)B);
   }
 }
 
@@ -600,9 +685,25 @@ extern "C" int ftg_activate_bwd(const float* dout, int lddo, const float* act, i
                                 const int* span_start, const int* span_width, const int* span_kind, float* dfake,
                                 int ldf, float tau, int accumulate, ftg_stream_t stream) {
   long long n_work = (long long)B * n_spans;
-  ftg_launch(k_activate_bwd, dim3(ftg_cdiv(n_work, 128)), dim3(128), 0, (cudaStream_t)stream, dout, lddo, act, lda, B, n_spans, span_start,
-                                                                          span_width, span_kind, dfake, ldf, 1.f / tau,
-                                                                          accumulate);
+  ftg_launch(k_activate_bwd, dim3(ftg_cdiv(n_work, 128)), dim3(128), 0, (cudaStream_t)stream, dout, lddo, act, lda, B,
+             n_spans, span_start, span_width, span_kind, dfake, ldf, 1.f / tau, accumulate, nullptr, 0, nullptr, 0, nullptr,
+             0, nullptr, nullptr, nullptr);
+  FTG_LAUNCH_CHECK();
+  return 0;
+}
+
+// backward of apply_activate + cond_loss value and gradient, one launch (+ one 4-byte memset)
+extern "C" int ftg_gen_output_bwd(const float* dout, int lddo, const float* act, int lda, int B, int n_spans,
+                                  const int* span_start, const int* span_width, const int* span_kind, float* dfake,
+                                  int ldf, float tau, const float* fake, int ldfk, const float* cond, int ldc,
+                                  const float* mask, int ldm, const int* col_soft, const int* soft_cstart,
+                                  float* loss_out, ftg_stream_t stream) {
+  cudaError_t e = cudaMemsetAsync(loss_out, 0, sizeof(float), (cudaStream_t)stream);
+  if (e != cudaSuccess) return (int)e;
+  long long n_work = (long long)B * n_spans;
+  ftg_launch(k_activate_bwd, dim3(ftg_cdiv(n_work, 128)), dim3(128), 0, (cudaStream_t)stream, dout, lddo, act, lda, B,
+             n_spans, span_start, span_width, span_kind, dfake, ldf, 1.f / tau, 0, fake, ldfk, cond, ldc, mask, ldm,
+             col_soft, soft_cstart, loss_out);
   FTG_LAUNCH_CHECK();
   return 0;
 }

@@ -31,9 +31,13 @@ __device__ __forceinline__ void sample_col_opt(const float* __restrict__ cum_p, 
 __global__ void __launch_bounds__(1024)
 k_prep_select(const float* __restrict__ cum_p, int n_col, int max_w, const int* __restrict__ soft_width,
               const int* __restrict__ soft_cstart, const int* __restrict__ row_ptr, const int* __restrict__ row_ids,
-              int* col, int* opt, int* perm, int* rid, int B, int P2, const int64_t* state, int s_col, int s_perm,
-              int s_row) {
+              int* col, int* opt, int* perm, int* rid, int B, int P2, int64_t* state, int s_col, int s_perm,
+              int s_row, int do_tick) {
   FTG_PDL_ENTER();
+  if (do_tick) {                       // first kernel of an iteration: advance the (seed, step) state
+    if (threadIdx.x == 0) state[1] += 1;
+    __syncthreads();
+  }
   extern __shared__ unsigned char smem_raw[];
   float* key = reinterpret_cast<float*>(smem_raw);
   int* idx = reinterpret_cast<int*>(key + P2);
@@ -142,15 +146,15 @@ __global__ void __launch_bounds__(128) k_prep_rows(const PrepRows P) {
 
 extern "C" int ftg_prep_select(const float* cum_p, int n_col, int max_w, const int* soft_width,
                                const int* soft_cstart, const int* row_ptr, const int* row_ids, int* col, int* opt,
-                               int* perm, int* rid, int B, const int64_t* rng_state, int s_col, int s_perm, int s_row,
-                               ftg_stream_t stream) {
+                               int* perm, int* rid, int B, int64_t* rng_state, int s_col, int s_perm, int s_row,
+                               int do_tick, ftg_stream_t stream) {
   int P2 = 1;
   while (P2 < B) P2 <<= 1;
   if (P2 > 4096) return FTG_ERR_UNSUPPORTED;
   int threads = P2 < 1024 ? (P2 < 32 ? 32 : P2) : 1024;
   ftg_launch(k_prep_select, dim3(1), dim3(threads), (size_t)P2 * 12, (cudaStream_t)stream, cum_p, n_col, max_w, soft_width, soft_cstart,
                                                                       row_ptr, row_ids, col, opt, perm, rid, B, P2,
-                                                                      rng_state, s_col, s_perm, s_row);
+                                                                      rng_state, s_col, s_perm, s_row, do_tick);
   FTG_LAUNCH_CHECK();
   return 0;
 }

@@ -185,7 +185,7 @@ class TrainEngine:
         t = self.table
         h0 = self.off[0]
         rng = self.rng
-        if inject is None and self.device.type == "cuda" and ops.native_available() and not ops._force_reference():
+        if self._fused_prep(inject):
             return self._prep_fused(with_real)
         R = lambda k: self._rand(inject, k, None)  # noqa: E731
         ops.fill_normal(self.h[:, h0:h0 + E], z=R(f"z_{prefix}"), rng=rng, stream=S_Z_D if with_real else S_Z_G)
@@ -205,6 +205,10 @@ class TrainEngine:
                               real[:, dd:dd + self.layout.n_opt], None, self.perm)
         return c1
 
+    def _fused_prep(self, inject):
+        return (inject is None and self.device.type == "cuda" and ops.native_available()
+                and not ops._force_reference())
+
     def _prep_fused(self, with_real):
         from ..ops import native
 
@@ -213,7 +217,7 @@ class TrainEngine:
         c1 = self.h[:, h0 + E:h0 + E + self.layout.n_opt]
         if with_real:
             native.prep_d_batch(self.table, self.tables, z, c1, self.X[B:2 * B], self.col, self.opt, self.perm,
-                                self.rid, self.rng, S_Z_D, S_COL_D, S_PERM, S_ROW)
+                                self.rid, self.rng, S_Z_D, S_COL_D, S_PERM, S_ROW, tick=True)
         else:
             native.prep_g_batch(self.table, self.tables, z, c1, self.m1, self.col, self.opt, self.rng, S_Z_G, S_COL_G)
         return c1
@@ -301,7 +305,8 @@ class TrainEngine:
         c1 = self._prep(inject, "d", with_real=True)
         self.g_forward(training=True)
         ops.activate_fwd(self.fake, self.tables, self.X[:B], tau=cfg.tau, u=self._rand(inject, "u_gumbel_d", None),
-                         rng=self.rng, stream=S_GUMBEL_D, cond=c1)
+                         rng=self.rng, stream=S_GUMBEL_D, cond=c1, slerp_real=self.X[B:2 * B, :din],
+                         slerp_out=self.X[2 * B:, :din], alpha=self._rand(inject, "alpha", None), slerp_stream=S_ALPHA)
         if prefetch_g:
             # The G step's batch preparation and generator forward only depend on buffers this D
             # step is done with (h, a, fake) and on G's weights, which the D step never changes:
@@ -309,8 +314,6 @@ class TrainEngine:
             with self.branch(2):
                 self._g_c1 = self._prep(inject, "g", with_real=False)
                 self.g_forward(training=True)
-        ops.slerp(self.X[B:2 * B, :din], self.X[:B, :din], self.X[2 * B:, :din],
-                  alpha=self._rand(inject, "alpha", None), rng=self.rng, stream=S_ALPHA)
         self.d_forward(3 * Bp, inject, "u_drop_d", S_DROP_D, self.rowscale_loss, self.loss_d, self.rowscale_d)
         # backward signals for all rows (interp rows carry the d y / d x seed)
         self.d_signals(3 * Bp, self.rowscale_d)
@@ -358,15 +361,16 @@ class TrainEngine:
         self.d_forward(Bp, inject, "u_drop_g", S_DROP_G, self.rowscale_g, self.loss_g_adv, self.rowscale_g)
         self.d_signals(Bp, self.rowscale_g)
         ops.linear(self.Z[0][:Bp], self._dw(0), self.dXp, b_t=True)
-        ops.activate_bwd(self.dX[:, :dd], self.X[:B, :dd], self.tables, self.dfake, tau=cfg.tau)
-        ops.cond_loss_fwd_bwd(self.fake, c1, self.m1, self.tables, self.dfake, self.ce, accumulate=True)
+        ops.gen_output_bwd(self.dX[:, :dd], self.X[:B, :dd], self.fake, c1, self.m1, self.tables, self.dfake, self.ce,
+                           tau=cfg.tau)
         self.g_backward()
         ops.adam_step(self.G.data[: self.G.n_trainable], self.G.grad, self.G.exp_avg, self.G.exp_avg_sq,
                       self.rng.state[1:2], lr=cfg.lr, beta1=cfg.betas[0], beta2=cfg.betas[1], eps=cfg.adam_eps,
                       weight_decay=cfg.l2scale)
 
     def iteration(self, inject=None):
-        self.rng.tick()
+        if not self._fused_prep(inject):
+            self.rng.tick()          # (the fused D-step prep kernel advances the step counter itself)
         overlap = self.concurrent
         self.d_step(inject, prefetch_g=overlap)
         self.g_step(inject, prefetched=overlap)

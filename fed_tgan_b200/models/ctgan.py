@@ -109,6 +109,8 @@ def calc_gradient_penalty(netD, real_data, fake_data, device="cpu", pac=10, lamb
     if alpha is None:
         alpha = torch.rand(real_data.size(0), 1, device=device)
     interpolates = slerp(alpha, real_data, fake_data)
+    if not interpolates.requires_grad:           # inputs without history (e.g. fake rows received over RPC)
+        interpolates.requires_grad_(True)
     disc = netD(interpolates)
     grads = torch.autograd.grad(
         outputs=disc, inputs=interpolates, grad_outputs=torch.ones_like(disc),

@@ -60,7 +60,11 @@ _ws_bytes = _sig("ftg_gemm_tc_workspace_bytes", [_i, _i, _i], _ll)
 _num_tiles = _sig("ftg_gemm_tc_num_tiles", [_i, _i])
 _rowdot = _sig("ftg_rowdot", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp])
 _rowdot_loss = _sig("ftg_rowdot_loss", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp])
-_prep_select = _sig("ftg_prep_select", [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp])
+_prep_select = _sig("ftg_prep_select", [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp])
+_act_fwd_slerp = _sig("ftg_activate_fwd_slerp", [_vp, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _f, _vp, _i, _vp, _i, _vp,
+                                                 _i, _i, _i, _vp, _i, _vp, _i, _vp, _i, _vp])
+_gen_out_bwd = _sig("ftg_gen_output_bwd", [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _f, _vp, _i, _vp, _i, _vp, _i,
+                                           _vp, _vp, _vp, _vp])
 _prep_rows = _sig("ftg_prep_rows", [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _vp, _i, _vp,
                                     _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _i, _vp, _i, _i, _vp])
 _d_head = _sig("ftg_d_head", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp])
@@ -273,13 +277,23 @@ def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta,
     return da
 
 
-def activate_fwd(fake, tables, out, *, tau=0.2, u=None, rng=None, stream=0, cond=None, hard_noise=True):
+def activate_fwd(fake, tables, out, *, tau=0.2, u=None, rng=None, stream=0, cond=None, hard_noise=True,
+                 slerp_real=None, slerp_out=None, alpha=None, slerp_stream=0):
     dd = tables["col_span"].numel()
     pf, ldf = _m(fake)
     po, ldo = _m(out)
     pu, ldu = _m(u)
     pc, ldc = _m(cond)
     n_opt = cond.shape[1] if cond is not None else 0
+    if slerp_real is not None:
+        pr, ldr = _m(slerp_real)
+        pi, ldi = _m(slerp_out)
+        _ck(_act_fwd_slerp(pf, ldf, fake.shape[0], dd, tables["span_start"].numel(), _p(tables["span_start"]),
+                           _p(tables["span_width"]), _p(tables["span_kind"]), _p(tables["col_span"]), po, ldo,
+                           float(tau), pu, ldu, _p(rng.state) if rng is not None else None, int(stream), pc, ldc,
+                           n_opt, int(hard_noise), pr, ldr, pi, ldi, _p(alpha), int(slerp_stream), _stream()),
+            "activate_fwd_slerp")
+        return out
     _ck(_act_fwd(pf, ldf, fake.shape[0], dd, tables["span_start"].numel(), _p(tables["span_start"]),
                  _p(tables["span_width"]), _p(tables["span_kind"]), _p(tables["col_span"]), po, ldo, float(tau), pu,
                  ldu, _p(rng.state) if rng is not None else None, int(stream), pc, ldc, n_opt, int(hard_noise),
@@ -294,6 +308,19 @@ def activate_bwd(dout, act, tables, dfake, *, tau=0.2, accumulate=False):
     _ck(_act_bwd(pd, ldd, pa, lda, dout.shape[0], tables["span_start"].numel(), _p(tables["span_start"]),
                  _p(tables["span_width"]), _p(tables["span_kind"]), pf, ldf, float(tau), int(accumulate), _stream()),
         "activate_bwd")
+    return dfake
+
+
+def gen_output_bwd(dout, act, fake, cond, mask, tables, dfake, loss_out, *, tau=0.2):
+    pd, ldd = _m(dout)
+    pa, lda = _m(act)
+    pdf, ldf = _m(dfake)
+    pfk, ldfk = _m(fake)
+    pc, ldc = _m(cond)
+    pm, ldm = _m(mask)
+    _ck(_gen_out_bwd(pd, ldd, pa, lda, dout.shape[0], tables["span_start"].numel(), _p(tables["span_start"]),
+                     _p(tables["span_width"]), _p(tables["span_kind"]), pdf, ldf, float(tau), pfk, ldfk, pc, ldc, pm,
+                     ldm, _p(tables["col_soft"]), _p(tables["soft_cstart"]), _p(loss_out), _stream()), "gen_output_bwd")
     return dfake
 
 
@@ -395,13 +422,15 @@ def prep_g_batch(table, tables, z_out, c_out, m_out, col, opt, rng, s_z, s_col):
                    int(s_z), int(s_col), _stream()), "prep_rows(G)")
 
 
-def prep_d_batch(table, tables, z_out, c_out, real_out, col, opt, perm, rid, rng, s_z, s_col, s_perm, s_row):
+def prep_d_batch(table, tables, z_out, c_out, real_out, col, opt, perm, rid, rng, s_z, s_col, s_perm, s_row,
+                 tick=False):
     """Fused D-step preparation: select kernel + per-row writer (z, c1, real row | c2)."""
     B = z_out.shape[0]
     dd = tables["col_span"].numel()
     _ck(_prep_select(_p(table.cum_p), table.cum_p.shape[0], table.cum_p.shape[1], _p(tables["soft_width"]),
                      _p(tables["soft_cstart"]), _p(table.row_ptr), _p(table.row_ids), _p(col), _p(opt), _p(perm),
-                     _p(rid), B, _p(rng.state), int(s_col), int(s_perm), int(s_row), _stream()), "prep_select")
+                     _p(rid), B, _p(rng.state), int(s_col), int(s_perm), int(s_row), int(tick), _stream()),
+        "prep_select")
     pz, ldz = _m(z_out)
     pc, ldc = _m(c_out)
     pr, ldr = _m(real_out)

@@ -164,7 +164,8 @@ def _gumbel_from_u(u):
     return -torch.log(-torch.log(u))
 
 
-def activate_fwd(fake, tables, out, *, tau=0.2, u=None, rng=None, stream=0, cond=None, hard_noise=True):
+def activate_fwd(fake, tables, out, *, tau=0.2, u=None, rng=None, stream=0, cond=None, hard_noise=True,
+                 slerp_real=None, slerp_out=None, alpha=None, slerp_stream=0):
     """``out[:, :data_dim] = apply_activate(fake)``; optionally ``out[:, data_dim:] = cond``.
 
     ``tables`` = ``TableLayout.device_tables``.  ``u`` are the uniforms behind the gumbel
@@ -187,7 +188,17 @@ def activate_fwd(fake, tables, out, *, tau=0.2, u=None, rng=None, stream=0, cond
             out[:, st:st + w] = torch.softmax((x[:, st:st + w] + noise[:, st:st + w]) / tau, dim=1)
     if cond is not None:
         out[:, dd:dd + cond.shape[1]] = cond
+    if slerp_real is not None:      # fused on the device: interpolates = slerp(alpha, real_cat, fake_cat)
+        din = slerp_real.shape[1]
+        slerp(slerp_real, out[:, :din], slerp_out, alpha=alpha, rng=rng, stream=slerp_stream)
     return out
+
+
+def gen_output_bwd(dout, act, fake, cond, mask, tables, dfake, loss_out, *, tau=0.2):
+    """``activate_bwd`` followed by the ``cond_loss`` value and gradient (one launch on the device)."""
+    activate_bwd(dout, act, tables, dfake, tau=tau)
+    cond_loss_fwd_bwd(fake, cond, mask, tables, dfake, loss_out, accumulate=True)
+    return dfake
 
 
 def activate_bwd(dout, act, tables, dfake, *, tau=0.2, accumulate=False):

@@ -83,9 +83,8 @@ class MDGANServer:
         self.start_epoch = 0
         self.round_times = []
         self._rid = 0
-        if self.group.is_root:
-            os.makedirs(self.models_dir, exist_ok=True)
-            os.makedirs(self.result_dir, exist_ok=True)
+        os.makedirs(self.models_dir, exist_ok=True)
+        os.makedirs(self.result_dir, exist_ok=True)
 
     # ------------------------------------------------------------ categorical
     def uniform_meta_category(self):
@@ -334,7 +333,8 @@ class MDGANServer:
     def sample_data(self, index, wait=True):
         """Generate ``cfg.sample_rows`` rows with the current global G and write
         ``<Name>_result/<Name>_synthesis_epoch_<index>.csv`` (reference ``:582-590``)."""
-        if not self.group.is_root:
+        self._sample_calls = getattr(self, "_sample_calls", -1) + 1
+        if not self.group.is_writer(self._sample_calls):
             return None
         if (not wait and self._writer is not None and self.group.generator_arena().device.type == "cuda"
                 and self.group.__class__.__name__ != "RpcGroup"):

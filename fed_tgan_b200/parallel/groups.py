@@ -51,6 +51,10 @@ class ClientGroup:
     def prepare(self):
         """Called once after the clients built their networks and before the first round."""
 
+    def is_writer(self, round_no: int) -> bool:
+        """Does this process generate + write the synthetic CSV of round ``round_no``?"""
+        return self.is_root
+
     def barrier(self):
         pass
 
@@ -169,7 +173,8 @@ class RpcGroup(ClientGroup):
 class SpmdGroup(ClientGroup):
     """Every rank owns one client; collective calls all-gather their results."""
 
-    def __init__(self, client, pg=None, use_symmetric=None):
+    def __init__(self, client, pg=None, use_symmetric=None, rotate_writers=True):
+        self.rotate_writers = rotate_writers
         self.client = client
         self.pg = pg
         self.rank = dist.get_rank(pg)
@@ -192,6 +197,14 @@ class SpmdGroup(ClientGroup):
 
     def run(self, method, *args):
         getattr(self.client, method)(*args)
+
+    def is_writer(self, round_no: int) -> bool:
+        # After aggregation every rank holds the same generator and the federator state is
+        # replicated, so the per-epoch generation + CSV duty rotates over the ranks instead of
+        # loading rank 0 every round (all ranks share the box's file system).
+        if self.rotate_writers:
+            return round_no % self.n == self.rank
+        return self.is_root
 
     def root_compute(self, fn):
         box = [fn() if self.is_root else None]

@@ -108,6 +108,17 @@ int ftg_activate_fwd(const float* fake, int ldf, int B, int dd, int n_spans, con
                      const int* span_width, const int* span_kind, const int* col_span, float* out, int ldo, float tau,
                      const float* u, int ldu, const int64_t* rng_state, int rng_stream, const float* cond,
                      int ldc, int n_opt, int use_noise, ftg_stream_t stream);
+/* activate + cat(c1) + slerp(alpha, real, fake_cat) in one launch (D step) */
+int ftg_activate_fwd_slerp(const float* fake, int ldf, int B, int dd, int n_spans, const int* span_start,
+                           const int* span_width, const int* span_kind, const int* col_span, float* out, int ldo,
+                           float tau, const float* u, int ldu, const int64_t* rng_state, int rng_stream,
+                           const float* cond, int ldc, int n_opt, int use_noise, const float* real, int ldr,
+                           float* interp, int ldi, const float* alpha, int alpha_stream, ftg_stream_t stream);
+/* backward of apply_activate fused with cond_loss value + gradient (G step) */
+int ftg_gen_output_bwd(const float* dout, int lddo, const float* act, int lda, int B, int n_spans,
+                       const int* span_start, const int* span_width, const int* span_kind, float* dfake, int ldf,
+                       float tau, const float* fake, int ldfk, const float* cond, int ldc, const float* mask, int ldm,
+                       const int* col_soft, const int* soft_cstart, float* loss_out, ftg_stream_t stream);
 int ftg_activate_bwd(const float* dout, int lddo, const float* act, int lda, int B, int n_spans,
                      const int* span_start, const int* span_width, const int* span_kind, float* dfake, int ldf,
                      float tau, int accumulate, ftg_stream_t stream);
@@ -148,7 +159,7 @@ int ftg_expand_rows(const float* vals, int n_tanh, const int* codes, int n_col, 
  * with its permuted cond vector (mode 1, D step). */
 int ftg_prep_select(const float* cum_p, int n_col, int max_w, const int* soft_width, const int* soft_cstart,
                     const int* row_ptr, const int* row_ids, int* col, int* opt, int* perm, int* rid, int B,
-                    const int64_t* rng_state, int s_col, int s_perm, int s_row, ftg_stream_t stream);
+                    int64_t* rng_state, int s_col, int s_perm, int s_row, int do_tick, ftg_stream_t stream);
 int ftg_prep_rows(int mode, int* col, int* opt, const int* perm, const int* rid, const int* soft_cstart,
                   float* z_out, int ldz, int E, float* c_out, int ldc, int n_opt, float* m_out, int ldm, int n_col,
                   const float* vals, int n_tanh, const int* codes, const int* tanh_start, const int* soft_start,

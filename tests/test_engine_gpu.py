@@ -111,3 +111,21 @@ def test_device_vgm_encode_matches_host_distribution():
     rt = t.inverse_transform(t.expand(dv, dc))
     inside = np.abs(dv).max(axis=1) < 0.99
     assert np.abs(rt[inside][:, [0, 2]] - data[inside][:, [0, 2]]).max() < 1e-2
+
+
+def test_fedavg_barrier_timeout_is_reported_not_hung():
+    """Failure detection: a rank whose peer never shows up at the in-kernel barrier gives up after
+    the timeout and raises on the host instead of hanging the GPU (single GPU: 'peer' = nobody)."""
+    from fed_tgan_b200.parallel.symm import SymmetricBlock
+
+    blk = SymmetricBlock(4096, "cuda:0")
+    other = SymmetricBlock(4096, "cuda:0")
+    blk.rank, blk.world = 0, 2
+    blk.peer_ptrs = [blk.ptr, other.ptr]
+    blk.peer_flag_ptrs = [blk.flag_ptr, other.flag_ptr]        # rank 1 never signals
+    before = blk.tensor.clone()
+    blk.fedavg([0.5, 0.5], 4096, [], 1, mode="twoshot", timeout_ms=30)
+    torch.cuda.synchronize()
+    with pytest.raises(RuntimeError, match="timed out"):
+        blk.check()
+    assert torch.equal(before, blk.tensor)                      # nothing was averaged

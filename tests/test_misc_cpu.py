@@ -150,3 +150,39 @@ def test_checkpoint_resume(tmp_path):
     path = s2.save_model("unit")
     obj = torch.load(path, weights_only=False)
     assert len(obj) == 5 and obj[3] == 100
+
+
+def test_legacy_mdgan_split_api():
+    """MD-GAN / GDTS mode: generator on the 'server', D trained on the client (reference
+    distributed.py:421-525).  The RRef is replaced by a local stand-in with the same surface."""
+    import torch
+    from fed_tgan_b200.models import ctgan
+
+    schema = get_schema("adult", rows=450)
+    df = make_table(schema, seed=4)
+    cfg = CTGANConfig(batch_size=100, gen_dim=(16, 16), dis_dim=(16, 16), embedding_dim=8, sample_rows=50)
+    c = MDGANClient(datapath="Adult_train.csv", selected_variables=schema.columns, categorical_list=schema.categorical,
+                    nonnegative_list=[], date_dic={}, target_column=schema.target, problem_type="", epochs=1,
+                    device="cpu", config=cfg, dataframe=df, write_side_files=False, vgm_backend="vb")
+    srv = MDGANServer([c], epochs=1, config=cfg, name="Adult", out_dir="/tmp", vgm_backend="vb", write_csv=False)
+    srv.uniform_meta_category(); srv.uniform_continuous_gmm(); srv.refit_local_transformer()
+    G = ctgan.Generator(cfg.embedding_dim + c.layout.n_opt, cfg.gen_dim, c.layout.data_dim)
+
+    class FakeRRef:
+        def rpc_sync(self):
+            return self
+
+        def forward(self, z):
+            with torch.no_grad():
+                return G(z)
+
+    c.register_G(FakeRRef())
+    before = {k: v.clone() for k, v in c.engine.D.to_module().state_dict().items()}
+    loss_d, pen = c.train_D()
+    assert torch.isfinite(loss_d) and torch.isfinite(pen) and len(c.time_train_d) == c.steps_per_epoch
+    after = c.discriminator.state_dict()
+    assert any(not torch.equal(before[k], after[k]) for k in before)
+    lg = c.loss_G()
+    assert torch.isfinite(torch.as_tensor(lg)) and len(c.time_loss_g) == c.steps_per_epoch
+    assert set(c.get_cond_generator()) >= {"cum_p", "cum_emp", "n_col", "n_opt"}
+    assert c.reset_on_cuda() is True

@@ -410,3 +410,32 @@ def test_fused_prep_and_heads(N):
     for k in range(3):
         close(outs[0][k], outs[1][k], 2e-5, 2e-5)
     assert outs[0][3].abs().max().item() < 1e-3          # analytically zero
+
+
+def test_fused_activate_slerp_and_output_bwd(N):
+    lay = _layout()
+    T = lay.device_tables(dev())
+    B, dd, n_opt = 500, lay.data_dim, lay.n_opt
+    din = dd + n_opt
+    ld = (din + 3) // 4 * 4
+    fake = padded(B, dd, (dd + 3) // 4 * 4, 1)
+    u = uni(B, dd, seed=2)
+    alpha = uni(B, seed=5)
+    cond = torch.zeros(B, n_opt, device=dev())
+    col = torch.randint(0, lay.n_col, (B,), device=dev())
+    opt = (torch.rand(B, device=dev()) * T["soft_width"][col]).long()
+    cond[torch.arange(B), T["soft_cstart"][col].long() + opt] = 1
+    m = torch.zeros(B, lay.n_col, device=dev()); m[torch.arange(B), col] = 1
+    X1 = rnd(3 * B, ld, seed=7).abs() + 0.1
+    X2 = X1.clone()
+    for fn, X in ((N.activate_fwd, X1), (R.activate_fwd, X2)):
+        fn(fake, T, X[:B], tau=0.2, u=u, cond=cond, slerp_real=X[B:2 * B, :din], slerp_out=X[2 * B:, :din], alpha=alpha)
+    close(X1[:B, :din], X2[:B, :din], 1e-4, 2e-5)
+    close(X1[2 * B:, :din], X2[2 * B:, :din], 2e-4, 1e-4)
+    assert torch.equal(X1[B:2 * B], X2[B:2 * B])
+    dout = rnd(B, dd, seed=3)
+    d1, d2 = torch.zeros(B, dd + 1, device=dev()), torch.zeros(B, dd + 1, device=dev())
+    l1, l2 = torch.zeros(1, device=dev()), torch.zeros(1, device=dev())
+    N.gen_output_bwd(dout, X2[:B, :dd], fake, cond, m, T, d1, l1, tau=0.2)
+    R.gen_output_bwd(dout, X2[:B, :dd], fake, cond, m, T, d2, l2, tau=0.2)
+    close(d1, d2, 1e-4, 1e-5); close(l1, l2, 1e-4, 1e-5)
