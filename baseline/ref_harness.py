@@ -67,10 +67,14 @@ def _spawn(spec, gpu, log):
     env = dict(os.environ)
     env["CUDA_VISIBLE_DEVICES"] = "" if gpu is None else str(gpu)
     env["PYTHONPATH"] = ""
-    # torchrun exports OMP_NUM_THREADS=1; the reference is CPU heavy, so give it the default threading back
-    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "GROUP_RANK", "LOCAL_WORLD_SIZE",
-              "TORCHELASTIC_RUN_ID", "OMP_NUM_THREADS"):
-        env.pop(k, None)
+    # Children must not inherit torchrun's environment: TORCHELASTIC_USE_AGENT_STORE makes the
+    # reference's own tcp:// rendezvous wait for a store nobody hosts (hang), and OMP_NUM_THREADS=1
+    # would throttle the CPU-heavy reference.
+    drop = ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT", "GROUP_RANK", "LOCAL_WORLD_SIZE",
+            "ROLE_RANK", "ROLE_WORLD_SIZE", "ROLE_NAME", "GROUP_WORLD_SIZE", "OMP_NUM_THREADS")
+    for k in list(env):
+        if k in drop or k.startswith("TORCHELASTIC") or k.startswith("TORCH_NCCL") or k.startswith("NCCL_ASYNC"):
+            env.pop(k, None)
     fh = open(log, "w")
     return subprocess.Popen([sys.executable, os.path.join(HERE, "ref_worker.py"), json.dumps(spec)],
                             env=env, stdout=fh, stderr=subprocess.STDOUT)
@@ -115,7 +119,14 @@ def run_reference_bench(args):
                             os.path.join(base, "server.log")))
     procs.append(_spawn(dict(common, rank=rank + 1, cwd=os.path.join(base, f"client{rank + 1}")), local,
                         os.path.join(base, f"client{rank + 1}.log")))
-    rc = [p.wait() for p in procs]
+    limit = 600 + 90 * epochs                      # generous; a healthy round takes ~30 s
+    rc = []
+    for p in procs:
+        try:
+            rc.append(p.wait(timeout=max(1, limit - (time.time() - t0))))
+        except subprocess.TimeoutExpired:
+            p.kill()
+            rc.append(-9)
     wall = time.time() - t0
     if world > 1:
         dist.barrier()
