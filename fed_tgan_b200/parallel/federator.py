@@ -279,7 +279,18 @@ class MDGANServer:
         self._slot_i = 0
         self._gen_graph = None
 
-    def _sample_data_async(self, index):
+    def warm_generation(self):
+        """One-time set-up of the asynchronous generation pipeline (pinned slots, CUDA-graph capture,
+        kernel module load) on every process that will ever be a writer, so that no round pays it."""
+        arena = self.group.generator_arena()
+        if self._writer is None or arena.device.type != "cuda" or self.group.__class__.__name__ == "RpcGroup":
+            return
+        if not any(self.group.is_writer(r) for r in range(max(self.group.n, 1))):
+            return
+        self._sample_data_async("warm", write=False)
+        self.drain()
+
+    def _sample_data_async(self, index, write=True):
         """Snapshot G, then generate + copy to pinned host memory on a side stream (one CUDA
         graph) while the caller goes on with the next round; a worker thread waits for the
         copy and writes the CSV."""
@@ -315,7 +326,7 @@ class MDGANServer:
 
         def finish(slot=slot, index=index):
             slot["done"].synchronize()
-            if self.write_csv:
+            if self.write_csv and write:
                 return self._decode_and_write(slot["host"].numpy(), index)
             return None
 
@@ -366,6 +377,7 @@ class MDGANServer:
     # ------------------------------------------------------------------ rounds
     def fit(self):
         self.group.prepare()
+        self.warm_generation()
         if self.resume:
             self._try_resume()
         w = np.asarray(self.weights_con_cat_combination, dtype=np.float64)

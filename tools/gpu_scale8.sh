@@ -2,9 +2,7 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=index,name --format=csv,noheader | head -8
-for N in 8 4 2; do
+for N in 8 4; do
   echo "== bench N=$N"
   timeout 500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29600+N)) bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.log 2>&1; echo "rc=$?"; tail -1 gpurun_out/bench_n$N.log | cut -c1-420
 done
-echo "== fedavg 8"
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29700 tools/fedavg_mgpu_check.py > gpurun_out/mgpu8.log 2>&1; echo "rc=$?"; grep -E "^\{|ALL OK|FAILED" gpurun_out/mgpu8.log | cut -c1-260
