@@ -439,3 +439,36 @@ def test_fused_activate_slerp_and_output_bwd(N):
     N.gen_output_bwd(dout, X2[:B, :dd], fake, cond, m, T, d1, l1, tau=0.2)
     R.gen_output_bwd(dout, X2[:B, :dd], fake, cond, m, T, d2, l2, tau=0.2)
     close(d1, d2, 1e-4, 1e-5); close(l1, l2, 1e-4, 1e-5)
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_gemm_never_writes_outside_its_output_view(N, prec):
+    """compute-sanitizer is closed on this pool, so out-of-bounds stores are hunted with canaries:
+    the output is a window inside a sentinel-filled buffer, for ragged shapes, all operand majors,
+    every epilogue specialisation and both split-K implementations."""
+    SENT = 12345.0
+    cases = [(150, 256, 640, False, False), (50, 250, 256, False, True), (130, 70, 150, True, True),
+             (500, 128, 764, False, False), (37, 19, 44, True, False)]
+    for M, Nn, K, a_t, b_t in cases:
+        r4 = lambda x: (x + 3) // 4 * 4  # noqa: E731
+        a = padded(K, M, r4(M), 1) if a_t else padded(M, K, r4(K), 1)
+        b = padded(K, Nn, r4(Nn), 2) if b_t else padded(Nn, K, r4(K), 2)
+        bias = rnd(Nn, seed=3)
+        mask = uni(M, r4(Nn), seed=4)[:, :Nn]
+        for epi in (dict(), dict(bias=bias), dict(mask_in=mask), dict(accumulate=True),
+                    dict(bias=bias, act="leaky_dropout", u=uni(M, r4(Nn), seed=5)[:, :Nn])):
+            for split in (None, 3):
+                if prec == "fp32" and split is not None:
+                    continue
+                big = torch.full((M + 4, r4(Nn) + 8), SENT, device=dev())
+                out = big[2:M + 2, 4:4 + Nn]
+                out.zero_()
+                kw = dict(epi)
+                if "act" in kw:
+                    kw["mask_out"] = torch.zeros(M, r4(Nn), device=dev())[:, :Nn]
+                N.linear(a, b, out, a_t=a_t, b_t=b_t, precision=prec, split_k=split, **kw)
+                torch.cuda.synchronize()
+                guard = big.clone()
+                guard[2:M + 2, 4:4 + Nn] = SENT
+                assert bool((guard == SENT).all()), (M, Nn, K, a_t, b_t, list(epi), split)
+                assert bool(torch.isfinite(out).all())
