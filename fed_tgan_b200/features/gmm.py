@@ -156,6 +156,7 @@ def fit_vbgmm_1d(
     tol: float = 1e-3,
     reg_covar: float = 1e-6,
     device=None,
+    use_kernel: bool = True,
 ):
     """Fit DP-GMMs to every row of ``x`` (``[C, n]``: C columns, n samples) at once.
 
@@ -166,7 +167,12 @@ def fit_vbgmm_1d(
     x = torch.as_tensor(np.asarray(x) if not torch.is_tensor(x) else x)
     if x.dim() == 1:
         x = x[None, :]
-    x = x.to(device=device or x.device, dtype=torch.float64)
+    dev = torch.device(device) if device is not None else x.device
+    if dev.type == "cuda" and n_components <= 12 and use_kernel:
+        fitted = _fit_vbgmm_kernel(x.to(dev), n_components, dp_prior, max_iter, tol, reg_covar)
+        if fitted is not None:
+            return fitted
+    x = x.to(device=dev, dtype=torch.float64)
     C, n = x.shape
     K = n_components
     eps10 = 10 * torch.finfo(torch.float64).eps
@@ -234,6 +240,21 @@ def fit_vbgmm_1d(
         w = w / w.sum()
         out.append(GMMParams(mu[c].copy(), cov[c].copy(), w, nu[c].copy(), kappa[c].copy(), a[c].copy(), b[c].copy()))
     return out
+
+
+def _fit_vbgmm_kernel(x, K, dp_prior, max_iter, tol, reg_covar):
+    """One CTA per column on the device (``csrc/vbgmm.cu``); ``None`` if the native library is missing."""
+    try:
+        from ..ops import native
+    except Exception:
+        return None
+    xf = x.to(torch.float32).contiguous()
+    srt = torch.sort(xf, dim=1).values
+    n = xf.shape[1]
+    q = ((torch.arange(K, device=xf.device, dtype=torch.float64) + 0.5) / K * (n - 1)).round().long()
+    out, _ = native.vbgmm_fit(xf, srt[:, q], dp_prior, max_iter, tol, reg_covar)
+    arr = out.cpu().numpy()
+    return [GMMParams.from_array(arr[c]) for c in range(arr.shape[0])]
 
 
 def fit_sklearn_1d(col: np.ndarray, n_components=10, dp_prior=1e-3, random_state=None) -> GMMParams:

@@ -97,6 +97,7 @@ _symm_export = _sig("ftg_symm_export", [_vp, C.c_char_p])
 _symm_open = _sig("ftg_symm_open", [C.c_char_p, C.POINTER(_vp)])
 _symm_close = _sig("ftg_symm_close", [_vp])
 _stats = _sig("ftg_stats_to_weights", [_vp, _i, _i, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp])
+_vbgmm = _sig("ftg_vbgmm_fit", [_vp, _i, _i, _vp, _i, C.c_double, _i, C.c_double, C.c_double, _i, _vp, _vp, _vp])
 _launch_count = _sig("ftg_last_launch_count", [])
 lib.ftg_version.restype = C.c_char_p
 
@@ -563,3 +564,17 @@ def stats_to_weights(hist, cat_off, pool_sorted, client_sorted, smp_off, rows):
                _p(client_sorted) if n_cont else None, _p(smp_off) if n_cont else None, n_cont, _p(rows), _p(jsd),
                _p(wd), _p(w), _stream()), "stats_to_weights")
     return jsd[:, :n_cat], wd[:, :n_cont], w
+
+
+def vbgmm_fit(x, init_centers, dp_prior=1e-3, max_iter=100, tol=1e-3, reg_covar=1e-6, lloyd_iters=16):
+    """Fit a K-component DP-GMM to every row of ``x`` ([C, n] fp32 CUDA); returns ([C, 7, K] fp64, iterations)."""
+    assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
+    Cn, n = x.shape
+    K = init_centers.shape[1]
+    ic = init_centers.to(device=x.device, dtype=torch.float32).contiguous()
+    out = torch.zeros(Cn, 7, K, dtype=torch.float64, device=x.device)
+    iters = torch.zeros(Cn, dtype=torch.int32, device=x.device)
+    with torch.cuda.device(x.device):
+        _ck(_vbgmm(_p(x), Cn, n, _p(ic), K, float(dp_prior), int(max_iter), float(tol), float(reg_covar),
+                   int(lloyd_iters), _p(out), _p(iters), _stream()), "vbgmm_fit")
+    return out, iters

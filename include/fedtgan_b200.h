@@ -176,6 +176,14 @@ int ftg_vgm_encode(const float* x, int rows, const float* logit_const, const flo
                    int k_active, const float* u, const int64_t* rng_state, int rng_stream, float* val_out,
                    int val_stride, int* code_out, int code_stride, ftg_stream_t stream);
 
+/* Variational-Bayes DP-GMM fit (sklearn BayesianGaussianMixture semantics, n_features = 1) of C
+ * columns at once, one CTA per column: x [C][n] fp32, init_centers [C][K] (k-means seeds, e.g.
+ * quantiles), out [C][7][K] fp64 = means, covs, weights, dof, mean_prec, wc_a, wc_b.  K <= 12.
+ * Replaces BayesianGaussianMixture.fit (S/dtds/features/transformers.py:334-340,
+ * S/dtds/distributed.py:725-746), SURVEY K14.                                              */
+int ftg_vbgmm_fit(const float* x, int C, int n, const float* init_centers, int K, double dp_prior, int max_iter,
+                  double tol, double reg_covar, int lloyd_iters, double* out, int* n_iter_out, ftg_stream_t stream);
+
 /* ---- federated weighted average (average_model, S/dtds/distributed.py:86-106 + the RPC
  *      gather/broadcast R9/R10), SURVEY K1 ------------------------------------------------
  * theta <- sum_i w_i theta_i written into every replica; `int_offsets` slots are truncated

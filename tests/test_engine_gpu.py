@@ -129,3 +129,29 @@ def test_fedavg_barrier_timeout_is_reported_not_hung():
     with pytest.raises(RuntimeError, match="timed out"):
         blk.check()
     assert torch.equal(before, blk.tensor)                      # nothing was averaged
+
+
+def test_vbgmm_kernel_matches_torch_fit():
+    from fed_tgan_b200.features.gmm import fit_vbgmm_1d
+
+    rng = np.random.default_rng(0)
+    n = 20000
+    cols = np.stack([
+        np.concatenate([rng.normal(0, 1, n // 2), rng.normal(8, 0.5, n // 4), rng.normal(-6, 2, n // 4)]),
+        rng.exponential(2.0, n),
+        rng.normal(3, 1, n),
+    ])
+    ker = fit_vbgmm_1d(cols, device="cuda:0", use_kernel=True)
+    ref = fit_vbgmm_1d(cols, device="cuda:0", use_kernel=False)
+    for k, r in zip(ker, ref):
+        ak, ar = k.weights > 0.005, r.weights > 0.005
+        assert abs(int(ak.sum()) - int(ar.sum())) <= 1, (k.weights, r.weights)
+        # mixture moments agree
+        mk, mr = (k.weights * k.means).sum(), (r.weights * r.means).sum()
+        vk = (k.weights * (k.covs + k.means ** 2)).sum() - mk ** 2
+        vr = (r.weights * (r.covs + r.means ** 2)).sum() - mr ** 2
+        assert abs(mk - mr) < 0.02 * (1 + abs(mr)) and abs(vk - vr) < 0.03 * (1 + vr)
+        assert abs(k.weights.sum() - 1) < 1e-9 and (k.covs > 0).all()
+    # posterior usable by the encoder
+    p = ker[0].predict_proba(cols[0][:100])
+    assert np.allclose(p.sum(1), 1, atol=1e-9)
