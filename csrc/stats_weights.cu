@@ -22,27 +22,40 @@ __global__ void k_distances(const float* __restrict__ hist, int world, int n_cat
   if (c < n_cat) {
     const int lo = cat_off[c], w = cat_off[c + 1] - lo;
     const int hist_len = cat_off[n_cat];
-    // totals
-    float tp = 0.f, tq = 0.f;
+    // totals (fp64: near-identical client distributions make the divergence a difference of
+    // almost equal terms, fp32 loses it and the per-column normalisation amplifies the error)
+    __shared__ double dred[32];
+    auto block_sum_d = [&](double v) {
+      const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      __syncthreads();
+      if (lane == 0) dred[wid] = v;
+      __syncthreads();
+      double t = 0.0;
+      for (int w2 = 0; w2 < nw; ++w2) t += dred[w2];
+      return t;
+    };
+    double tp = 0.0, tq = 0.0;
     for (int k = threadIdx.x; k < w; k += blockDim.x) {
-      float g = 0.f;
+      double g = 0.0;
       for (int r = 0; r < world; ++r) g += hist[(size_t)r * hist_len + lo + k];
       tq += g;
       tp += hist[(size_t)i * hist_len + lo + k];
     }
-    tp = block_sum(tp, red);
-    tq = block_sum(tq, red);
-    float acc = 0.f;
+    tp = block_sum_d(tp);
+    tq = block_sum_d(tq);
+    double acc = 0.0;
     for (int k = threadIdx.x; k < w; k += blockDim.x) {
-      float g = 0.f;
+      double g = 0.0;
       for (int r = 0; r < world; ++r) g += hist[(size_t)r * hist_len + lo + k];
-      float q = g / tq, p = hist[(size_t)i * hist_len + lo + k] / tp;
-      float m = 0.5f * (p + q);
-      if (p > 0.f) acc += p * logf(p / m);
-      if (q > 0.f) acc += q * logf(q / m);
+      const double q = g / tq, p = (double)hist[(size_t)i * hist_len + lo + k] / tp;
+      const double m = 0.5 * (p + q);
+      if (p > 0.0) acc += p * log(p / m);
+      if (q > 0.0) acc += q * log(q / m);
     }
-    acc = block_sum(acc, red);
-    if (threadIdx.x == 0) jsd[(size_t)i * n_cat + c] = sqrtf(fmaxf(0.5f * acc, 0.f));
+    acc = block_sum_d(acc);
+    if (threadIdx.x == 0) jsd[(size_t)i * n_cat + c] = (float)sqrt(fmax(0.5 * acc, 0.0));
   } else {
     const int cc = c - n_cat;
     const float* pool = pool_sorted + (size_t)cc * n_total;

@@ -472,3 +472,28 @@ def test_gemm_never_writes_outside_its_output_view(N, prec):
                 guard[2:M + 2, 4:4 + Nn] = SENT
                 assert bool((guard == SENT).all()), (M, Nn, K, a_t, b_t, list(epi), split)
                 assert bool(torch.isfinite(out).all())
+
+
+def test_stats_kernel_near_identical_histograms(N):
+    """Binary columns whose client distributions differ in the 4th digit (Covertype-like): the
+    per-column normalised JSD must still match the fp64 host restatement."""
+    from fed_tgan_b200.parallel import weights as W
+
+    rng = np.random.default_rng(3)
+    world, n_cat = 2, 12
+    rows = np.array([250000.0, 331012.0], dtype=np.float32)
+    hist = []
+    for i in range(world):
+        parts = []
+        for c in range(n_cat):
+            p = 0.03 + 0.9 * (c / n_cat) + 1e-4 * rng.normal()
+            k = float(np.round(rows[i] * p))
+            parts.append(np.array([rows[i] - k, k], dtype=np.float32))
+        hist.append(np.concatenate(parts))
+    cat_off = (np.arange(n_cat + 1) * 2).astype(np.int32)
+    t = lambda x: torch.as_tensor(x).to(dev())  # noqa: E731
+    jsd, wd, wt = N.stats_to_weights(t(np.stack(hist)), t(cat_off), None, None, None, t(rows))
+    cv = [[h[cat_off[c]:cat_off[c + 1]].astype(np.float64) for h in hist] for c in range(n_cat)]
+    jr = W.categorical_similarity(cv)
+    assert np.allclose(jsd.cpu().numpy(), jr, atol=2e-3), (jsd.cpu().numpy(), jr)
+    assert np.allclose(wt.cpu().numpy(), W.final_weights(jr, np.zeros((world, 0)), rows), atol=1e-3)
