@@ -19,7 +19,9 @@ class GraphedIteration:
         assert dev.type == "cuda"
         from ..ops import native
 
-        self.stream = torch.cuda.Stream(device=dev)
+        # High-priority stream: the iteration's tiny latency-bound kernels must not queue behind the
+        # federator's big generation GEMMs that run concurrently on a default-priority stream.
+        self.stream = torch.cuda.Stream(device=dev, priority=-1)
         self.stream.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(self.stream):
             native.preallocate_scratch(dev)
@@ -37,7 +39,11 @@ class GraphedIteration:
         self.replays = 0
 
     def run(self, steps: int):
-        for _ in range(int(steps)):
-            self.graph.replay()
+        cur = torch.cuda.current_stream(self.engine.device)
+        self.stream.wait_stream(cur)
+        with torch.cuda.stream(self.stream):
+            for _ in range(int(steps)):
+                self.graph.replay()
+        cur.wait_stream(self.stream)
         self.replays += int(steps)
         self.engine.iterations += int(steps)

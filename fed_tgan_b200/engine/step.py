@@ -84,7 +84,7 @@ class TrainEngine:
         self.tables = layout.device_tables(dev)
         # independent kernels of an iteration run on side streams (parallel graph branches)
         self.concurrent = dev.type == "cuda"
-        self.side_streams = [torch.cuda.Stream(device=dev) for _ in range(3)] if self.concurrent else []
+        self.side_streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(3)] if self.concurrent else []
 
         B, P = cfg.batch_size, cfg.pack
         Bp = B // P
