@@ -310,6 +310,9 @@ class MDGANServer:
         self._gen_stream.wait_stream(cur)
         with torch.cuda.stream(self._gen_stream):
             self._snap.data.copy_(arena.data, non_blocking=True)
+            snap_done = torch.cuda.Event()
+            snap_done.record(self._gen_stream)
+            cur.wait_event(snap_done)         # the next round may overwrite the arena only after the snapshot
             if self._gen_graph is None:
                 from ..ops import native
 

@@ -186,3 +186,51 @@ def test_legacy_mdgan_split_api():
     assert torch.isfinite(torch.as_tensor(lg)) and len(c.time_loss_g) == c.steps_per_epoch
     assert set(c.get_cond_generator()) >= {"cum_p", "cum_emp", "n_col", "n_opt"}
     assert c.reset_on_cuda() is True
+
+
+def test_arena_padding_stays_zero_and_layout_roundtrip():
+    """Weights are stored with K padded to 4 floats (and the packed first D layer with per-row
+    padding); padding must stay exactly zero through training, and state_dict round-trips."""
+    import torch
+    from fed_tgan_b200.engine import DeviceTable, TrainEngine
+
+    rng = np.random.default_rng(0)
+    info = [(1, "tanh"), (3, "softmax"), (5, "softmax"), (2, "softmax")]      # data_dim 11, n_opt 10 -> din 21 (padded to 24)
+    lay = TableLayout(info)
+    vals = rng.uniform(-1, 1, (200, 1)).astype(np.float32)
+    codes = np.stack([rng.integers(0, w, 200) for w in lay.soft_width], 1).astype(np.int32)
+    cfg = CTGANConfig(batch_size=40, pack=10, gen_dim=(16, 16), dis_dim=(16, 16), embedding_dim=7)
+    eng = TrainEngine(cfg, lay, DeviceTable(vals, codes, lay), "cpu")
+    for arena in (eng.G, eng.D):
+        used = torch.zeros(arena.numel, dtype=torch.bool)
+        for k in arena.slots:
+            used[arena._index(k)] = True
+        assert (~used).any()                                   # there is padding in this configuration
+        eng.train(3)
+        assert bool((arena.data[~used] == 0).all())
+        sd = arena.state_dict()
+        arena2 = type(arena)(cfg, lay, "cpu", init=False)
+        arena2.load_state_dict(sd)
+        assert torch.equal(arena2.data, arena.data)
+        ref = arena.reference_module().state_dict()
+        assert list(sd.keys()) == list(ref.keys()) and all(sd[k].shape == ref[k].shape and sd[k].dtype == ref[k].dtype for k in ref)
+
+
+def test_native_csv_writer_matches_pandas(tmp_path):
+    from fed_tgan_b200.ops import hostlib
+
+    if not hostlib.available():
+        import pytest
+        pytest.skip("native library not built")
+    rng = np.random.default_rng(1)
+    n = 5000
+    cols = [rng.normal(size=n).astype(np.float32), (rng.integers(0, 3, n).astype(np.int32), ["a", "b,c", " "]),
+            rng.integers(-5, 5, n), rng.normal(size=n) * 1e-7]
+    names = ["x", "cat", "i", "tiny"]
+    hostlib.write_csv(str(tmp_path / "n.csv"), names, cols, n_threads=3)
+    back = pd.read_csv(tmp_path / "n.csv", keep_default_na=False)
+    assert list(back.columns) == names and len(back) == n
+    assert np.array_equal(back["x"].to_numpy(np.float32), cols[0])
+    assert list(back["cat"]) == [cols[1][1][c] for c in cols[1][0]]
+    assert np.array_equal(back["i"].to_numpy(), cols[2])
+    assert np.allclose(back["tiny"].to_numpy(), cols[3], rtol=1e-15, atol=0)
