@@ -238,7 +238,8 @@ def run_ours(args):
             "clients": n_clients, "split": mode, "global_batch": cfg.batch_size * n_clients, "batch_per_client": cfg.batch_size,
             "seq_len": None, "local_steps_per_round": steps_per_epoch, "rows_per_client": len(shard),
             "sample_rows_per_round": cfg.sample_rows, "parallelism": f"federated-dp{n_clients}",
-            "aggregation": "fused two-shot NVLink kernel" if world > 1 else "single client (reference short-circuit)",
+            "aggregation": ("fused NVLS multimem kernel" if os.environ.get("FEDTGAN_AGGREGATION") == "nvls"
+                            else "fused two-shot NVLink kernel") if world > 1 else "single client (reference short-circuit)",
             "l2": "flushed between rounds (192 MB memset)" if flush is not None else "not flushed",
             "csv_writer": "rotates over ranks" if (world > 1 and args.rotate) else "rank 0 (async side stream + writer pool)",
             "baseline_ref": "README demo 24.2 s/round (Intrusion, 2 clients, unknown HW)",

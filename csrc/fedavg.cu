@@ -212,6 +212,104 @@ k_fedavg_oneshot(Peers P, float* staging, int rank, int world, long long n4, Int
     reinterpret_cast<float4*>(mine)[q] = reinterpret_cast<const float4*>(staging)[q];
 }
 
+// ------------------------------------------------------------------- NVLS
+// Same aggregation through the NVSwitch multicast engine: every rank first scales its own
+// replica by w_rank in place, then rank r pulls shard r already summed by the switch
+// (multimem.ld_reduce) and pushes the result to all replicas with one multicast store
+// (multimem.st).  Per GPU that halves the NVLink traffic of the P2P two-shot kernel
+// ((N-1)/N*P out, P/N + (N-1)/N*P in).  The reduction order inside the switch is not
+// specified, so this variant is not bitwise reproducible across runs (replicas are still
+// identical to each other: everybody receives the same multicast value).
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__global__ void __launch_bounds__(512)
+k_fedavg_nvls(Peers P, float* mc_base, int rank, int world, long long n4, IntSlots slots, int round_id, int* status,
+              unsigned long long timeout_ns) {
+  const unsigned long long deadline = globaltimer_ns() + timeout_ns;
+  int* myflags = P.f[rank];
+  __shared__ int s_last;
+  // phase 0: theta_rank *= w_rank (whole local replica), then tell the peers
+  {
+    float4* mine = reinterpret_cast<float4*>(P.p[rank]);
+    const float w = P.w[rank];
+    const long long stride0 = (long long)gridDim.x * blockDim.x;
+    for (long long q0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < n4; q0 += stride0 * 4) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (q0 + u * stride0 < n4) v[u] = mine[q0 + u * stride0];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (q0 + u * stride0 < n4) {
+          v[u].x *= w; v[u].y *= w; v[u].z *= w; v[u].w *= w;
+          mine[q0 + u * stride0] = v[u];
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int done = atomicAdd(myflags + 2 * world, 1);
+      s_last = (done == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last) {
+      if (threadIdx.x == 0) myflags[2 * world] = 0;
+      __threadfence_system();
+      signal_peers(P, rank, world, 0, round_id);
+    }
+  }
+  if (!wait_peers(P, rank, world, 0, round_id, deadline)) {
+    if (threadIdx.x == 0) atomicExch(status, 1);
+    return;
+  }
+  // phase 1: in-switch reduce of my shard, multicast the result into every replica
+  const long long chunk = (n4 + world - 1) / world;
+  const long long lo = (long long)rank * chunk, hi = min(n4, lo + chunk);
+  {
+    constexpr int U = 4;                      // independent switch reductions in flight per thread
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long q0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < hi; q0 += stride * U) {
+      float4 acc[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long q = q0 + u * stride;
+        if (q < hi) acc[u] = multimem_ld_reduce_add(mc_base + q * 4);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long q = q0 + u * stride;
+        if (q < hi) {
+          if (slots.n) acc[u] = trunc_slots(acc[u], q * 4, slots);
+          multimem_st(mc_base + q * 4, acc[u]);
+        }
+      }
+    }
+  }
+  // phase 2: barrier-out
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int done = atomicAdd(myflags + 2 * world + 2, 1);
+    s_last = (done == (int)gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  if (threadIdx.x == 0) myflags[2 * world + 2] = 0;
+  __threadfence_system();
+  signal_peers(P, rank, world, 1, round_id);
+  if (!wait_peers(P, rank, world, 1, round_id, deadline)) {
+    if (threadIdx.x == 0) atomicExch(status, 2);
+  }
+}
+
 int fill(Peers& P, IntSlots& S, float* const* arenas, int* const* flags, int world, const float* weights,
          const int* int_offsets, int n_int) {
   if (world < 1 || world > MAX_WORLD || n_int > MAX_INT) return FTG_ERR_UNSUPPORTED;
@@ -279,6 +377,23 @@ extern "C" int ftg_fedavg_oneshot(float* const* peers, int* const* flags, float*
   if (blocks > 128) blocks = 128;          // CTAs spin on a local flag: must all be resident
   k_fedavg_oneshot<<<blocks, 256, 0, (cudaStream_t)stream>>>(P, staging, rank, world, n4, S, round_id, status,
                                                              (unsigned long long)timeout_ms * 1000000ull);
+  FTG_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int ftg_fedavg_nvls(float* const* peers, int* const* flags, float* multicast_base, int rank, int world,
+                               const float* weights, long long n, const int* int_offsets, int n_int, int round_id,
+                               int* status, int timeout_ms, ftg_stream_t stream) {
+  Peers P; IntSlots S;
+  int rc = fill(P, S, peers, flags, world, weights, int_offsets, n_int);
+  if (rc) return rc;
+  if ((n & 3) || !multicast_base) return FTG_ERR_UNSUPPORTED;
+  long long n4 = n / 4;
+  int blocks = ftg_cdiv(n4, 512 * 4);
+  if (blocks > 144) blocks = 144;          // CTAs meet at grid-wide counters: keep them co-resident
+  if (blocks < 1) blocks = 1;
+  k_fedavg_nvls<<<blocks, 512, 0, (cudaStream_t)stream>>>(P, multicast_base, rank, world, n4, S, round_id, status,
+                                                          (unsigned long long)timeout_ms * 1000000ull);
   FTG_LAUNCH_CHECK();
   return 0;
 }

@@ -91,6 +91,7 @@ _vgm_encode = _sig("ftg_vgm_encode", [_vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, 
 _fedavg_local = _sig("ftg_fedavg_local", [_vp, _i, _vp, _ll, _vp, _i, _vp])
 _fedavg_twoshot = _sig("ftg_fedavg_twoshot", [_vp, _vp, _i, _i, _vp, _ll, _vp, _i, _i, _vp, _i, _vp])
 _fedavg_oneshot = _sig("ftg_fedavg_oneshot", [_vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _i, _i, _vp, _i, _vp])
+_fedavg_nvls = _sig("ftg_fedavg_nvls", [_vp, _vp, _vp, _i, _i, _vp, _ll, _vp, _i, _i, _vp, _i, _vp])
 _symm_alloc = _sig("ftg_symm_alloc", [_ll, C.POINTER(_vp)])
 _symm_free = _sig("ftg_symm_free", [_vp])
 _symm_export = _sig("ftg_symm_export", [_vp, C.c_char_p])
@@ -522,6 +523,15 @@ def fedavg_oneshot(peer_ptrs, flag_ptrs, staging, rank, weights, n, int_offsets,
     io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
     _ck(_fedavg_oneshot(pa, fa, _p(staging), rank, world, w, n, io, len(int_offsets), int(round_id), _p(status),
                         int(timeout_ms), _stream()), "fedavg_oneshot")
+
+
+def fedavg_nvls(peer_ptrs, flag_ptrs, multicast_ptr, rank, weights, n, int_offsets, round_id, status, timeout_ms=20000):
+    world = len(peer_ptrs)
+    pa, fa = _ptr_array(peer_ptrs), _ptr_array(flag_ptrs)
+    w = (C.c_float * world)(*[float(x) for x in weights])
+    io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
+    _ck(_fedavg_nvls(pa, fa, multicast_ptr, rank, world, w, n, io, len(int_offsets), int(round_id), _p(status),
+                     int(timeout_ms), _stream()), "fedavg_nvls")
 
 
 def symm_alloc(nbytes):

@@ -295,6 +295,22 @@ class MDGANClient:
         return self.symm.export_handle()
 
     @_on_device
+    def symm_setup_nvls(self, group=None):
+        """Collective (SPMD only): put the arenas into a multicast-bound symmetric allocation so the
+        aggregation can run through the NVSwitch reduction engine (``ftg_fedavg_nvls``)."""
+        from .symm import NvlsBlock
+
+        e = self.engine
+        self.symm = NvlsBlock(e.G.numel + e.D.numel, self.device, group)
+        g_store = self.symm.tensor[: e.G.numel]
+        d_store = self.symm.tensor[e.G.numel: e.G.numel + e.D.numel]
+        g_old, d_old = e.G.data.clone(), e.D.data.clone()
+        self._build_engine(g_store, d_store)
+        self.engine.G.data.copy_(g_old)
+        self.engine.D.data.copy_(d_old)
+        return True
+
+    @_on_device
     def symm_connect(self, rank, handles):
         self.symm.connect(rank, handles)
         return True

@@ -17,6 +17,9 @@ over three transports:
 
 from __future__ import annotations
 
+import os
+import warnings
+
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -222,6 +225,16 @@ class SpmdGroup(ClientGroup):
             self._setup_symmetric()
 
     def _setup_symmetric(self):
+        # FEDTGAN_AGGREGATION=nvls: in-switch reduction (multimem) instead of the P2P two-shot
+        # kernel; measured only marginally faster at 8 GPUs / 168 MB and slower below that
+        # (profiles/fedavg_mgpu_8_nvls.json), and not run-to-run bitwise reproducible -> opt-in.
+        if os.environ.get("FEDTGAN_AGGREGATION", "twoshot") == "nvls":
+            try:
+                self.client.symm_setup_nvls(self.pg)
+                self._symm_ready = True
+                return
+            except RuntimeError as exc:
+                warnings.warn(f"NVLS aggregation unavailable ({exc}); using the P2P two-shot kernel")
         handle = self.client.symm_export()
         handles = [None] * self.n
         dist.all_gather_object(handles, handle, group=self.pg)

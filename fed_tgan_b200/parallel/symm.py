@@ -85,3 +85,50 @@ class SymmetricBlock:
             except Exception:
                 pass
         self._opened = []
+
+
+class NvlsBlock:
+    """Multicast-bound symmetric block (``torch.distributed._symmetric_memory`` does the
+    cuMulticast* / fabric-handle plumbing); the aggregation itself is our ``ftg_fedavg_nvls``
+    kernel.  Collective constructor: every rank of ``group`` must call it.  Raises
+    ``RuntimeError`` if the platform exposes no multicast pointer (NVLS unavailable)."""
+
+    def __init__(self, n_floats: int, device, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from ..ops import native
+
+        self.native = native
+        self.device = torch.device(device)
+        self.n_floats = (int(n_floats) + 31) // 32 * 32
+        group = group if group is not None else dist.group.WORLD
+        with torch.cuda.device(self.device):
+            self._all = symm_mem.empty(self.n_floats + FLAG_INTS, dtype=torch.float32, device=self.device)
+            self._all.zero_()
+            self.hdl = symm_mem.rendezvous(self._all, group)
+        self.rank, self.world = self.hdl.rank, self.hdl.world_size
+        mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
+        if mc == 0:
+            raise RuntimeError("NVLS multicast is not available on this platform")
+        self.multicast_ptr = mc
+        self.tensor = self._all[: self.n_floats]
+        self.peer_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.peer_flag_ptrs = [p + self.n_floats * 4 for p in self.peer_ptrs]
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        dist.barrier(group=group)
+
+    def fedavg(self, weights, n, int_offsets, round_id, mode="nvls", timeout_ms=20000):
+        n = (int(n) + 3) // 4 * 4
+        with torch.cuda.device(self.device):
+            if mode == "nvls":
+                self.native.fedavg_nvls(self.peer_ptrs, self.peer_flag_ptrs, self.multicast_ptr, self.rank, weights, n,
+                                        int_offsets, round_id, self.status, timeout_ms)
+            else:
+                self.native.fedavg_twoshot(self.peer_ptrs, self.peer_flag_ptrs, self.rank, weights, n, int_offsets,
+                                           round_id, self.status, timeout_ms)
+
+    def check(self):
+        code = int(self.status.item())
+        if code:
+            raise RuntimeError(f"fedavg peer barrier timed out (phase {code})")

@@ -206,6 +206,13 @@ int ftg_fedavg_oneshot(float* const* peers, int* const* flags, float* staging, i
                        const float* weights, long long n, const int* int_offsets, int n_int, int round_id,
                        int* status, int timeout_ms, ftg_stream_t stream);
 
+/* NVLS variant: replicas live in a multicast-bound symmetric allocation; each rank pre-scales its
+ * replica by w_rank, then shard r is summed inside the NVSwitch (multimem.ld_reduce.add.f32) and
+ * multicast back to all replicas (multimem.st).  Not bitwise reproducible (switch sum order). */
+int ftg_fedavg_nvls(float* const* peers, int* const* flags, float* multicast_base, int rank, int world,
+                    const float* weights, long long n, const int* int_offsets, int n_int, int round_id,
+                    int* status, int timeout_ms, ftg_stream_t stream);
+
 /* peer-memory plumbing (cudaMalloc + CUDA IPC); the only allocating entry points */
 int ftg_symm_alloc(long long bytes, void** ptr);
 int ftg_symm_free(void* ptr);

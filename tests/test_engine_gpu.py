@@ -155,3 +155,22 @@ def test_vbgmm_kernel_matches_torch_fit():
     # posterior usable by the encoder
     p = ker[0].predict_proba(cols[0][:100])
     assert np.allclose(p.sum(1), 1, atol=1e-9)
+
+
+@pytest.mark.gpu
+def test_nvls_aggregation_two_gpus():
+    """NVSwitch multimem variant of the aggregation kernel vs the torch sum on 2 ranks (needs 2 GPUs)."""
+    import os
+    import subprocess
+    import sys
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if not k.startswith(("TORCHELASTIC", "RANK", "LOCAL_RANK", "WORLD_SIZE"))}
+    env["FEDAVG_MODES"] = "nvls"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29631", os.path.join(root, "tools", "fedavg_mgpu_check.py")]
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "ALL OK" in out.stdout

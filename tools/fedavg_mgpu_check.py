@@ -14,7 +14,9 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from fed_tgan_b200.parallel.symm import SymmetricBlock  # noqa: E402
+from fed_tgan_b200.parallel.symm import NvlsBlock, SymmetricBlock  # noqa: E402
+
+MODES = os.environ.get("FEDAVG_MODES", "twoshot,oneshot").split(",")
 
 rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"]); local = int(os.environ.get("LOCAL_RANK", rank))
 torch.cuda.set_device(local)
@@ -23,16 +25,25 @@ dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 
 sizes = [1_005_472, 2_900_000, 8_000_000, 42_000_000]      # floats: Adult G+D, Intrusion, ..., wide 1024 nets
 n_max = max(sizes)
-blk = SymmetricBlock(n_max, dev)
+ipc_blk = SymmetricBlock(n_max, dev)
 handles = [None] * world
-dist.all_gather_object(handles, blk.export_handle())
-blk.connect(rank, handles)
+dist.all_gather_object(handles, ipc_blk.export_handle())
+ipc_blk.connect(rank, handles)
 dist.barrier()
+nvls_blk = None
+if "nvls" in MODES:
+    try:
+        nvls_blk = NvlsBlock(n_max, dev)
+    except Exception as exc:                                   # noqa: BLE001
+        if rank == 0:
+            print(json.dumps({"mode": "nvls", "unavailable": repr(exc)[:300]}), flush=True)
+        MODES = [m for m in MODES if m != "nvls"]
 w = torch.softmax(torch.arange(world, dtype=torch.float64) * 0.3, 0).tolist()
 round_id = 0
 results = []
 ok_all = True
-for mode in ("twoshot", "oneshot"):
+for mode in MODES:
+    blk = nvls_blk if mode == "nvls" else ipc_blk
     for n in sizes:
         n4 = n // 4 * 4
         g = torch.Generator(device="cpu").manual_seed(100 + rank)
@@ -79,15 +90,15 @@ for mode in ("twoshot", "oneshot"):
             nt.append(s.elapsed_time(e))
         tn = torch.tensor(sorted(nt)[len(nt) // 2], device=dev, dtype=torch.float64)
         dist.all_reduce(tn, op=dist.ReduceOp.MAX)
-        bytes_link = 2 * (world - 1) / world * n4 * 4 if mode == "twoshot" else (world - 1) * n4 * 4
+        bytes_link = (world - 1) * n4 * 4 if mode == "oneshot" else 2 * (world - 1) / world * n4 * 4
         row = {"mode": mode, "world": world, "floats": n4, "max_err": err, "replicas_equal": equal, "ok": ok,
-               "ms": float(t), "nccl_ms": float(tn), "nvlink_GBps_per_gpu": bytes_link / 2 / (float(t) * 1e-3) / 1e9 if mode == "twoshot" else bytes_link / (float(t) * 1e-3) / 1e9}
+               "ms": float(t), "nccl_ms": float(tn), "nvlink_GBps_per_gpu": bytes_link / (float(t) * 1e-3) / 1e9 if mode == "oneshot" else bytes_link / 2 / (float(t) * 1e-3) / 1e9}
         results.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
 if rank == 0:
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    with open(os.path.join(ROOT, "gpurun_out", f"fedavg_mgpu_{world}.json"), "w") as fh:
+    with open(os.path.join(ROOT, "gpurun_out", f"fedavg_mgpu_{world}{'_nvls' if 'nvls' in MODES else ''}.json"), "w") as fh:
         json.dump(results, fh, indent=1)
     print("ALL OK" if ok_all else "FAILED")
 dist.barrier()
