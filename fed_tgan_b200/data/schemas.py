@@ -85,12 +85,16 @@ def get_schema(name: str, rows: int | None = None) -> TableSchema:
     return s
 
 
-def make_table(schema: TableSchema, seed=0, rows=None, skew: float = 0.0) -> pd.DataFrame:
+def make_table(schema: TableSchema, seed=0, rows=None, skew: float = 0.0, correlated: float = 0.0) -> pd.DataFrame:
     """Random table of the schema.  ``skew`` in [0,1) tilts category frequencies and mode
-    weights (used to build non-IID client shards)."""
+    weights (used to build non-IID client shards).  ``correlated`` > 0 redraws the target
+    column from a logistic model over the latent codes (mode / category index) of the first
+    few feature columns, so that classifiers have something to learn (ML-utility runs); the
+    default keeps all columns independent (benchmarks only need the shapes)."""
     rng = np.random.default_rng(seed)
     n = int(rows if rows is not None else schema.rows)
     data = {}
+    codes = {}
     cats = dict(zip(schema.categorical, schema.cat_sizes))
     base_rng = np.random.default_rng(12345)     # column-level structure is shared across shards
     for ci, col in enumerate(schema.columns):
@@ -103,6 +107,16 @@ def make_table(schema: TableSchema, seed=0, rows=None, skew: float = 0.0) -> pd.
                 tilt = rng.dirichlet(np.ones(k) * 0.8)
                 p = (1 - skew) * p + skew * tilt
             ids = rng.choice(k, size=n, p=p / p.sum())
+            codes[col] = (ids, k, p / p.sum())
+            if correlated > 0 and col == schema.target:
+                struct = np.random.default_rng(4242)
+                logits = np.tile(np.log(p / p.sum()), (n, 1))
+                drivers = [c for c in schema.columns if c != col and c in codes][:4]
+                for d in drivers:
+                    d_ids, d_k, _ = codes[d]
+                    logits += correlated * struct.normal(0, 1.5, size=(d_k, k))[d_ids]
+                g = rng.gumbel(size=logits.shape)
+                ids = np.argmax(logits + g, axis=1)
             if col == "class" or schema.name != "Intrusion":
                 data[col] = np.array([f"{col}_v{i}" for i in range(k)], dtype=object)[ids]
             else:
@@ -115,6 +129,7 @@ def make_table(schema: TableSchema, seed=0, rows=None, skew: float = 0.0) -> pd.
             if skew > 0:
                 w = (1 - skew) * w + skew * rng.dirichlet(np.ones(m) * 0.8)
             comp = rng.choice(m, size=n, p=w / w.sum())
+            codes[col] = (comp, m, w / w.sum())
             x = rng.normal(mu[comp], sd[comp])
             if col in schema.nonnegative:
                 x = np.round(np.exp(np.abs(x)))          # heavy-tailed non-negative integers

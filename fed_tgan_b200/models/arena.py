@@ -108,11 +108,14 @@ class ParamArena:
     # ------------------------------------------------------------------ views
     def _view_of(self, base: torch.Tensor, name: str):
         s = self.slots[name]
+        # as_strided offsets are absolute in the underlying storage: ``base`` may itself be a
+        # slice of a larger block (D sits behind G in the symmetric allocation)
+        off = base.storage_offset() + s.offset
         if len(s.shape) == 2:
-            return torch.as_strided(base, (s.rows, s.cols), (s.ld, 1), s.offset)
+            return torch.as_strided(base, (s.rows, s.cols), (s.ld, 1), off)
         if len(s.shape) == 1:
-            return torch.as_strided(base, (s.cols,), (1,), s.offset)
-        return torch.as_strided(base, (1,), (1,), s.offset)
+            return torch.as_strided(base, (s.cols,), (1,), off)
+        return torch.as_strided(base, (1,), (1,), off)
 
     def view(self, name):
         """Physical view for kernels: 2-D ``[rows, cols]`` with row stride ``ld``."""

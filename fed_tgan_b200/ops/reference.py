@@ -24,7 +24,10 @@ TINY = 1e-10
 # ------------------------------------------------------------------ random state
 class RngState:
     """Seed + step counter.  On CUDA the counter lives in device memory so that CUDA-graph
-    replays advance it; on CPU it backs a ``torch.Generator``."""
+    replays advance it and the Philox kernels key every draw by (seed, step, site).  The
+    torch restatement draws from a ``torch.Generator`` that is re-seeded from (seed, step) at
+    every tick, so on both paths the random stream is a pure function of the two checkpointed
+    integers (bit-exact resume)."""
 
     def __init__(self, seed: int, device):
         self.seed = int(seed)
@@ -32,7 +35,12 @@ class RngState:
         # [seed, step] as int64 in device memory (read by kernels)
         self.state = torch.tensor([self.seed, 0], dtype=torch.int64, device=self.device)
         self.gen = torch.Generator(device="cpu")
-        self.gen.manual_seed(self.seed)
+        self.resync()
+
+    def resync(self):
+        """Re-derive the host generator from ``state`` (after a tick or a checkpoint load)."""
+        step = int(self.state[1])
+        self.gen.manual_seed((self.seed * 0x9E3779B1 + step * 0x85EBCA77 + 0x27D4EB2F) & 0x7FFFFFFFFFFFFFFF)
 
     def uniform(self, *shape):
         return torch.rand(*shape, generator=self.gen).to(self.device)
@@ -49,6 +57,7 @@ class RngState:
                 native.tick(self.state)
                 return
         self.state[1] += 1
+        self.resync()
 
 
 # ------------------------------------------------------------------------ GEMM

@@ -274,6 +274,8 @@ class MDGANClient:
         e.G.load_optimizer_state(st["optG"])
         e.D.load_optimizer_state(st["optD"])
         e.rng.state.copy_(st["rng"].to(e.rng.state.device))
+        e.rng.seed = int(st["rng"][0])
+        e.rng.resync()
         e.iterations = int(st.get("iterations", 0))
         return True
 
@@ -286,13 +288,19 @@ class MDGANClient:
         e = self.engine
         need = e.G.numel + e.D.numel
         self.symm = SymmetricBlock(need, self.device)
-        g_store = self.symm.tensor[: e.G.numel]
-        d_store = self.symm.tensor[e.G.numel: e.G.numel + e.D.numel]
-        g_old, d_old = e.G.data.clone(), e.D.data.clone()
-        self._build_engine(g_store, d_store)
-        self.engine.G.data.copy_(g_old)
-        self.engine.D.data.copy_(d_old)
+        self._rebind_storage(self.symm.tensor)
         return self.symm.export_handle()
+
+    def _rebind_storage(self, block):
+        """Move both arenas into ``block`` (G first, then D), keeping weights, Adam moments, the
+        Philox counter and the iteration count, and rebuild the engine over the new storage."""
+        e = self.engine
+        st = self.checkpoint_state()
+        g_raw, d_raw = e.G.data.clone(), e.D.data.clone()
+        self._build_engine(block[: e.G.numel], block[e.G.numel: e.G.numel + e.D.numel])
+        self.load_checkpoint_state(st)
+        self.engine.G.data.copy_(g_raw)          # bit-exact weights, padding included
+        self.engine.D.data.copy_(d_raw)
 
     @_on_device
     def symm_setup_nvls(self, group=None):
@@ -302,12 +310,7 @@ class MDGANClient:
 
         e = self.engine
         self.symm = NvlsBlock(e.G.numel + e.D.numel, self.device, group)
-        g_store = self.symm.tensor[: e.G.numel]
-        d_store = self.symm.tensor[e.G.numel: e.G.numel + e.D.numel]
-        g_old, d_old = e.G.data.clone(), e.D.data.clone()
-        self._build_engine(g_store, d_store)
-        self.engine.G.data.copy_(g_old)
-        self.engine.D.data.copy_(d_old)
+        self._rebind_storage(self.symm.tensor)
         return True
 
     @_on_device
@@ -324,6 +327,8 @@ class MDGANClient:
         self.symm.fedavg(weights, e.G.numel + e.D.numel, ints, round_id)
         if sync:
             self.symm.check()        # raises if a peer never arrived at the in-kernel barrier
+        else:
+            self.symm.poll()         # same, one round late, without a host-device sync
         return True
 
     # ------------------------------------- legacy MD-GAN / GDTS split-training API

@@ -287,7 +287,7 @@ class MDGANServer:
         """One-time set-up of the asynchronous generation pipeline (pinned slots, CUDA-graph capture,
         kernel module load) on every process that will ever be a writer, so that no round pays it."""
         arena = self.group.generator_arena()
-        if self._writer is None or arena.device.type != "cuda" or self.group.__class__.__name__ == "RpcGroup":
+        if self._writer is None or arena.device.type != "cuda" or not self.group.local_generator:
             return
         if not any(self.group.is_writer(r) for r in range(max(self.group.n, 1))):
             return
@@ -355,7 +355,7 @@ class MDGANServer:
         if not self.group.is_writer(self._sample_calls):
             return None
         if (not wait and self._writer is not None and self.group.generator_arena().device.type == "cuda"
-                and self.group.__class__.__name__ != "RpcGroup"):
+                and self.group.local_generator):
             return self._sample_data_async(index)
         t0 = time.time()
         dev_table = self.sample(self.cfg.sample_rows)

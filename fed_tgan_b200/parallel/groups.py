@@ -30,6 +30,10 @@ from ..ops import reference as ref_ops
 class ClientGroup:
     n: int
     is_root: bool = True
+    # True when generator_arena() is the live training arena on this process' GPU (the
+    # federator may then snapshot it and generate asynchronously); False when it is a copy
+    # fetched over the control plane.
+    local_generator: bool = True
 
     def call(self, method, *args, per_client=None):
         raise NotImplementedError
@@ -117,6 +121,8 @@ class LocalGroup(ClientGroup):
 
 
 class RpcGroup(ClientGroup):
+    local_generator = False
+
     def __init__(self, rrefs, use_symmetric=False, server_device="cpu"):
         self.rrefs = list(rrefs)
         self.n = len(self.rrefs)
@@ -216,6 +222,8 @@ class SpmdGroup(ClientGroup):
         return box[0]
 
     def barrier(self):
+        if self._symm_ready:
+            self.client.symm.check()
         dist.barrier(group=self.pg)
 
     def prepare(self):

@@ -23,7 +23,40 @@ class _CudaBlob:
         }
 
 
-class SymmetricBlock:
+class _StatusWord:
+    """Host side of the kernels' status word (0 = ok, 1/2 = barrier phase that timed out)."""
+
+    status: torch.Tensor
+    device: torch.device
+    _host_status = None
+    _status_evt = None
+
+    def check(self):
+        """Blocking: synchronise and raise if any launch so far gave up at a barrier."""
+        code = int(self.status.item())
+        if code:
+            raise RuntimeError(f"fedavg peer barrier timed out (phase {code})")
+
+    def poll(self):
+        """Non-blocking: raise if a status copy enqueued by an earlier ``poll`` has landed with an
+        error, then enqueue the next copy.  Called once per round, so a rank that missed a barrier
+        surfaces one round later without ever stalling the launch thread."""
+        if self._host_status is None:
+            self._host_status = torch.zeros(1, dtype=torch.int32).pin_memory()
+        if self._status_evt is not None:
+            if not self._status_evt.query():
+                return
+            self._status_evt = None
+            code = int(self._host_status[0])
+            if code:
+                raise RuntimeError(f"fedavg peer barrier timed out (phase {code})")
+        with torch.cuda.device(self.device):
+            self._host_status.copy_(self.status, non_blocking=True)
+            self._status_evt = torch.cuda.Event()
+            self._status_evt.record()
+
+
+class SymmetricBlock(_StatusWord):
     def __init__(self, n_floats: int, device):
         from ..ops import native
 
@@ -73,11 +106,6 @@ class SymmetricBlock:
                 self.native.fedavg_oneshot(self.peer_ptrs, self.peer_flag_ptrs, self.staging, self.rank, weights, n,
                                            int_offsets, round_id, self.status, timeout_ms)
 
-    def check(self):
-        code = int(self.status.item())
-        if code:
-            raise RuntimeError(f"fedavg peer barrier timed out (phase {code})")
-
     def close(self):
         for p in self._opened:
             try:
@@ -87,7 +115,7 @@ class SymmetricBlock:
         self._opened = []
 
 
-class NvlsBlock:
+class NvlsBlock(_StatusWord):
     """Multicast-bound symmetric block (``torch.distributed._symmetric_memory`` does the
     cuMulticast* / fabric-handle plumbing); the aggregation itself is our ``ftg_fedavg_nvls``
     kernel.  Collective constructor: every rank of ``group`` must call it.  Raises
@@ -127,8 +155,3 @@ class NvlsBlock:
             else:
                 self.native.fedavg_twoshot(self.peer_ptrs, self.peer_flag_ptrs, self.rank, weights, n, int_offsets,
                                            round_id, self.status, timeout_ms)
-
-    def check(self):
-        code = int(self.status.item())
-        if code:
-            raise RuntimeError(f"fedavg peer barrier timed out (phase {code})")

@@ -10,7 +10,8 @@ from fed_tgan_b200.features.layout import TableLayout
 from fed_tgan_b200.models import ctgan
 
 
-def small_setup(device="cpu", batch=40, pack=10, rows=300, seed=0, gen_dim=(32, 32), dis_dim=(24, 16), emb=12):
+def small_setup(device="cpu", batch=40, pack=10, rows=300, seed=0, gen_dim=(32, 32), dis_dim=(24, 16), emb=12,
+                block=False):
     rng = np.random.default_rng(seed)
     output_info = [(1, "tanh"), (3, "softmax"), (5, "softmax"), (1, "tanh"), (2, "softmax"), (4, "softmax")]
     layout = TableLayout(output_info)
@@ -18,7 +19,21 @@ def small_setup(device="cpu", batch=40, pack=10, rows=300, seed=0, gen_dim=(32, 
     codes = np.stack([rng.integers(0, w, size=rows) for w in layout.soft_width], axis=1).astype(np.int32)
     cfg = CTGANConfig(embedding_dim=emb, gen_dim=gen_dim, dis_dim=dis_dim, batch_size=batch, pack=pack, seed=seed)
     table = DeviceTable(vals, codes, layout, device)
-    eng = TrainEngine(cfg, layout, table, device)
+    if not block:
+        eng = TrainEngine(cfg, layout, table, device)
+        return cfg, layout, table, eng
+    # both arenas inside one allocation, behind a non-zero offset (the symmetric-memory layout)
+    from fed_tgan_b200.models.arena import DiscriminatorArena, GeneratorArena
+
+    probe = TrainEngine(cfg, layout, table, device)
+    ng, nd = probe.G.numel, probe.D.numel
+    buf = torch.full((64 + ng + nd + 64,), float("nan"), device=device)
+    G = GeneratorArena(cfg, layout, device, storage=buf[64: 64 + ng], seed=seed)
+    D = DiscriminatorArena(cfg, layout, device, storage=buf[64 + ng: 64 + ng + nd], seed=seed + 1)
+    eng = TrainEngine(cfg, layout, table, device, G, D, seed=seed)
+    eng.G.data.copy_(probe.G.data)
+    eng.D.data.copy_(probe.D.data)
+    eng._block = buf
     return cfg, layout, table, eng
 
 

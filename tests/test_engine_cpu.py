@@ -36,6 +36,29 @@ def test_iteration_matches_autograd():
             assert _close(eng.D.state_dict()[k].float(), v.float(), 1e-4), (it, "D param", k)
 
 
+def test_arenas_inside_one_block_match_autograd():
+    """G and D laid out back to back inside one allocation at a non-zero offset (how they sit in the
+    peer-mapped block): every kernel-facing view must address its own arena, nothing outside."""
+    cfg, lay, table, eng = small_setup(block=True)
+    G, D = eng.G.to_module(), eng.D.to_module()
+    G.train(); D.train()
+    optG = torch.optim.Adam(G.parameters(), lr=cfg.lr, betas=cfg.betas, weight_decay=cfg.l2scale)
+    optD = torch.optim.Adam(D.parameters(), lr=cfg.lr, betas=cfg.betas)
+    assert eng.D.view("seq.0.weight").data_ptr() >= eng.D.data.data_ptr()
+    for it in range(2):
+        inj = make_inject(eng, seed=20 + it)
+        ref = oracle_iteration(eng, inj, G, D, optG, optD)
+        eng.iteration(inj)
+        for k, v in ref["d_grads"].items():
+            assert _close(eng.D.grad_state_dict()[k], v), (it, "D grad", k)
+        for k, v in D.state_dict().items():
+            assert _close(eng.D.state_dict()[k].float(), v.float(), 1e-4), (it, "D param", k)
+        for k, v in G.state_dict().items():
+            assert _close(eng.G.state_dict()[k].float(), v.float(), 1e-4), (it, "G param", k)
+    guard = eng._block
+    assert torch.isnan(guard[:64]).all() and torch.isnan(guard[-64:]).all()      # nothing spilled outside
+
+
 def test_three_layer_nets():
     cfg, lay, table, eng = small_setup(gen_dim=(16, 24, 8), dis_dim=(16, 12, 8), batch=20, pack=5)
     G, D = eng.G.to_module(), eng.D.to_module()

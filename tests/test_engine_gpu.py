@@ -45,6 +45,20 @@ def test_iteration_native_vs_reference(precision, tol):
         assert perr <= (2e-4 if precision == "fp32" else 1.5e-3), (name, "param", perr)
 
 
+def test_iteration_with_arenas_in_one_block():
+    """Same iteration with G and D back to back inside one allocation (symmetric-memory layout): the
+    kernels must see exactly the same weights as with stand-alone arenas."""
+    kw = dict(batch=500, pack=10, rows=3000, gen_dim=(256, 256), dis_dim=(256, 256), emb=128)
+    ref = _run("tf32", False, **kw)
+    got = _run("tf32", False, block=True, **kw)
+    for k, v in ref.losses().items():
+        assert abs(v - got.losses()[k]) <= 1e-5 * (1 + abs(v)), k
+    assert (ref.G.data - got.G.data).abs().max().item() <= 1e-6
+    assert (ref.D.data - got.D.data).abs().max().item() <= 1e-6
+    guard = got._block
+    assert torch.isnan(guard[:64]).all() and torch.isnan(guard[-64:]).all()
+
+
 def test_graph_replay_trains():
     from fed_tgan_b200.engine.graph import GraphedIteration
 
@@ -128,6 +142,10 @@ def test_fedavg_barrier_timeout_is_reported_not_hung():
     torch.cuda.synchronize()
     with pytest.raises(RuntimeError, match="timed out"):
         blk.check()
+    blk.poll()                                                  # enqueues the asynchronous status copy
+    torch.cuda.synchronize()
+    with pytest.raises(RuntimeError, match="timed out"):
+        blk.poll()                                              # ... whose result is seen by the next poll
     assert torch.equal(before, blk.tensor)                      # nothing was averaged
 
 

@@ -56,3 +56,33 @@ def test_single_client_shortcut(tmp_path):
     federate(server, verbose=False)
     assert np.allclose(server.weights_con_cat_combination, [1.0])
     assert os.path.exists(tmp_path / "Adult_result" / "Adult_synthesis_epoch_0.csv")
+
+
+def test_rebinding_arena_storage_keeps_training_state(tmp_path):
+    """Moving the arenas into another block (what happens when the symmetric allocation is set up)
+    must not reset weights, Adam moments, the RNG counter or the iteration count: replaying an
+    epoch from the same state gives bit-identical results with and without a rebind in between."""
+    import torch
+
+    schema = get_schema("adult", rows=600)
+    df = make_table(schema, seed=3)
+    cfg = CTGANConfig(batch_size=50, gen_dim=(16, 16), dis_dim=(16,), embedding_dim=8, sample_rows=60, pack=5)
+    c = _clients(schema, [df], cfg)[0]
+    server = MDGANServer([c], epochs=1, config=cfg, name="Adult", out_dir=str(tmp_path), async_csv=False)
+    server.uniform_meta_category(); server.uniform_continuous_gmm(); server.refit_local_transformer()
+    c.run_local_epochs(1)
+    start = c.checkpoint_state()
+    c.run_local_epochs(1)
+    want = c.checkpoint_state()
+    c.load_checkpoint_state(start)
+    block = torch.full((c.engine.G.numel + c.engine.D.numel + 64,), float("nan"))
+    c._rebind_storage(block)
+    assert c.engine.G.data.data_ptr() == block.data_ptr()
+    c.run_local_epochs(1)
+    got = c.checkpoint_state()
+    for net in ("G", "D"):
+        for k in want[net]:
+            assert torch.equal(want[net][k], got[net][k]), (net, k)
+        assert torch.equal(want["opt" + net]["exp_avg"], got["opt" + net]["exp_avg"])
+        assert want["opt" + net]["step"] == got["opt" + net]["step"]
+    assert torch.equal(want["rng"], got["rng"]) and want["iterations"] == got["iterations"]

@@ -3,6 +3,12 @@ synthetic table and IID split, 2 clients, both arms on one GPU.  Writes
 gpurun_out/parity_<config>.json.
 
     python tools/parity_run.py [epochs] [config] [seeds]
+
+Environment: PARITY_CORRELATED=<float> makes the target column depend on four feature columns and
+adds the ML-utility gap (difference in weighted F1, real-trained minus synthetic-trained, mean over
+LR/DT/RF/MLP, tested on a held-out table) of the last epoch's CSV; PARITY_TAG names the output file;
+PARITY_ARMS=ours,reference selects arms.  Without a GPU both arms run on the CPU (ours through the
+torch restatement of the kernels, fp32).
 """
 import json
 import os
@@ -31,10 +37,28 @@ config = sys.argv[2] if len(sys.argv) > 2 else "adult"
 seeds = int(sys.argv[3]) if len(sys.argv) > 3 else 2
 n_clients = 2
 schema = get_schema(config)
-df = make_table(schema, seed=0)
+correlated = float(os.environ.get("PARITY_CORRELATED", "0"))
+tag = os.environ.get("PARITY_TAG", config)
+arms = os.environ.get("PARITY_ARMS", "ours,reference").split(",")
+df = make_table(schema, seed=0, correlated=correlated)
+df_test = make_table(schema, seed=1, rows=10000, correlated=correlated) if correlated > 0 else None
 shards = split_table(df, n_clients, "iid", seed=0)
 dev = "cuda:0" if torch.cuda.is_available() else "cpu"
-out = {"config": config, "epochs": epochs, "clients": n_clients, "rows": len(df), "ours": [], "reference": []}
+out = {"config": config, "epochs": epochs, "clients": n_clients, "rows": len(df), "device": dev,
+       "correlated_target": correlated, "ours": [], "reference": []}
+
+
+def utility_gap(result_dir, name):
+    if df_test is None:
+        return None
+    import pandas as pd
+
+    from fed_tgan_b200.eval.utility import utility_difference
+
+    fake = pd.read_csv(os.path.join(result_dir, f"{name}_synthesis_epoch_{epochs - 1}.csv"))
+    fake.columns = list(df.columns)
+    diff, f1 = utility_difference(df, df_test, fake, schema.categorical, schema.target, verbose=False)
+    return {"delta_f1": f1, "delta_acc_f1_per_model": np.asarray(diff).tolist()}
 
 
 def curves(result_dir, name):
@@ -45,7 +69,7 @@ def curves(result_dir, name):
     return res
 
 
-for seed in range(seeds):
+for seed in range(seeds if "ours" in arms else 0):
     # ---------------- ours
     base = tempfile.mkdtemp(prefix="parity_ours_")
     cfg = CTGANConfig(seed=seed)
@@ -60,10 +84,11 @@ for seed in range(seeds):
     c = curves(os.path.join(base, f"{schema.name}_result"), schema.name)
     out["ours"].append({"seed": seed, "wall_s": round(time.time() - t0, 1), "avg_jsd": [x[0] for x in c],
                         "avg_wd": [x[1] for x in c], "round_s": server.round_times,
-                        "weights": [float(w) for w in server.weights_con_cat_combination]})
-    print("ours seed", seed, "final JSD/WD", c[-1], flush=True)
+                        "weights": [float(w) for w in server.weights_con_cat_combination],
+                        "utility": utility_gap(os.path.join(base, f"{schema.name}_result"), schema.name)})
+    print("ours seed", seed, "final JSD/WD", c[-1], out["ours"][-1]["utility"] and out["ours"][-1]["utility"]["delta_f1"], flush=True)
 
-for seed in range(seeds):
+for seed in range(seeds if "reference" in arms else 0):
     # ---------------- reference (its own run(); torch/numpy seeds are whatever it draws)
     base = tempfile.mkdtemp(prefix="parity_ref_")
     ref_harness._prepare_dirs(base, schema, df, shards)
@@ -81,8 +106,9 @@ for seed in range(seeds):
     c = curves(os.path.join(base, "server", "Intrusion_result"), "Intrusion")
     times = [float(x) for x in open(os.path.join(base, "server", "timestamp_experiment.csv")).read().split()]
     out["reference"].append({"seed": seed, "wall_s": round(time.time() - t0, 1), "avg_jsd": [x[0] for x in c],
-                             "avg_wd": [x[1] for x in c], "round_s": times})
-    print("reference seed", seed, "final JSD/WD", c[-1], flush=True)
+                             "avg_wd": [x[1] for x in c], "round_s": times,
+                             "utility": utility_gap(os.path.join(base, "server", "Intrusion_result"), "Intrusion")})
+    print("reference seed", seed, "final JSD/WD", c[-1], out["reference"][-1]["utility"] and out["reference"][-1]["utility"]["delta_f1"], flush=True)
 
 
 def summary(arm):
@@ -93,10 +119,12 @@ def summary(arm):
     return {"final_avg_jsd_mean": float(j[:, -1].mean()), "final_avg_jsd_std": float(j[:, -1].std()),
             "final_avg_wd_mean": float(w[:, -1].mean()), "final_avg_wd_std": float(w[:, -1].std()),
             "epoch0_avg_jsd": float(j[:, 0].mean()), "epoch0_avg_wd": float(w[:, 0].mean()),
-            "mean_round_s": float(np.mean([np.mean(r["round_s"][1:]) for r in out[arm]]))}
+            "delta_f1_mean": (float(np.mean([r["utility"]["delta_f1"] for r in out[arm]])) if out[arm][0].get("utility") else None),
+            "delta_f1_std": (float(np.std([r["utility"]["delta_f1"] for r in out[arm]])) if out[arm][0].get("utility") else None),
+            "mean_round_s": float(np.mean([np.mean(r["round_s"][1:]) for r in out[arm]])) if epochs > 1 else None}
 
 
 out["summary"] = {"ours": summary("ours"), "reference": summary("reference")}
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"parity_{config}.json"), "w"), indent=1)
+json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"parity_{tag}.json"), "w"), indent=1)
 print(json.dumps(out["summary"], indent=1))

@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from fed_tgan_b200 import ops  # noqa: E402
-from fed_tgan_b200.config import CTGANConfig  # noqa: E402
+from fed_tgan_b200.config import CTGANConfig, wide_config  # noqa: E402
 from fed_tgan_b200.data.schemas import get_schema, make_table  # noqa: E402
 from fed_tgan_b200.ops import native  # noqa: E402
 from fed_tgan_b200.parallel.client import MDGANClient  # noqa: E402
@@ -29,7 +29,7 @@ native.set_precision(prec)
 dev = torch.device("cuda:0")
 schema = get_schema(cfgname, rows=48842 if cfgname == "adult" else 20000)
 df = make_table(schema, seed=0)
-cfg = CTGANConfig()
+cfg = wide_config() if cfgname == "wide" else CTGANConfig()
 client = MDGANClient(datapath=f"{schema.name}_train.csv", selected_variables=schema.columns,
                      categorical_list=schema.categorical, nonnegative_list=schema.nonnegative, date_dic={},
                      target_column=schema.target, problem_type="", epochs=1, device=dev, config=cfg, dataframe=df,
