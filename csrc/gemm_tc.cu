@@ -18,17 +18,19 @@
 #include <cuda.h>
 #include <mutex>
 #include <cstdio>
+#include <cstdlib>
 
 namespace {
 
 constexpr int BM = 128, BN = 64, BK = 32;       // BK floats = 128 B = one swizzle row
-constexpr int STAGES = 6;
+constexpr int MAX_STAGES = 6;                   // ring depth is a launch parameter (2..6), see choose_stages()
 constexpr int A_STAGE_BYTES = BM * BK * 4;      // 16 KB
 constexpr int B_STAGE_BYTES = BN * BK * 4;      //  8 KB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int TMEM_COLS = 64;
 constexpr int NUM_THREADS = 192;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int smem_bytes(int stages) { return stages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/; }
+constexpr int SMEM_BYTES = smem_bytes(MAX_STAGES);
 constexpr uint32_t SPIN_LIMIT = 1u << 24;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -183,11 +185,13 @@ __device__ long long g_gemm_timeline[16];
 __device__ int g_gemm_timeline_on = 0;
 #define TL(i) do { if (g_gemm_timeline_on && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) g_gemm_timeline[i] = clock64(); } while (0)
 
+// 112 registers: two (or three) CTAs fit one SM when the ring is shallow, so that on multi-wave
+// grids one CTA's prologue / epilogue latency hides under its neighbours' main loops.
 template <bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __maxnreg__(112)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
           const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters,
-          int vec_ok_i, int cluster_mode) {
+          int vec_ok_i, int cluster_mode, int STAGES) {
   const bool vec_ok = vec_ok_i != 0;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -431,6 +435,19 @@ EncodeTiledFn get_encode() {
   return fn;
 }
 
+// L2 promotion of the TMA requests.  A box row is 128 B; the next 128 B of the same row is the next
+// k-block (K-major) or the next 32-row chunk of the same stage (MN-major), so promoting a miss to
+// 256 B turns every other request into an L2 hit and doubles the DRAM burst per opened page.
+// FTG_TMA_L2_PROMO=128|256 overrides (experiments).
+CUtensorMapL2promotion l2_promotion() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("FTG_TMA_L2_PROMO");
+    v = e ? atoi(e) : 128;
+  }
+  return v == 256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+}
+
 // 2-D fp32 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld floats.
 bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, int box_inner, int box_outer,
               bool mn_major) {
@@ -443,9 +460,35 @@ bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, 
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE,
                    mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   l2_promotion(),
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;
+}
+
+// Ring depth (measured: tools/gemm_stage_sweep.py, profiles/gemm_stage_sweep.json).
+//  * A grid that fits the machine in one wave gets the deepest ring its k-loop can use: every k-block
+//    in flight at once (the CTGAN iteration is latency bound).
+//  * Multi-wave grids get 4 stages (99 KB) so that two CTAs are resident per SM and the SM overlaps
+//    one tile's prologue / epilogue with its neighbour's main loop: wgrad of the wide first
+//    discriminator layer (3936 tiles of 5 k-blocks) 165 -> 102 us, its dgrad (492 tiles) 70 -> 50 us.
+//    Three CTAs per SM (3 stages) is no better than two.
+//  * Clusters of 8 with one CTA per SM need 8 free SMs of one GPC each; 16 such clusters do not all
+//    fit, so a 128-CTA split-8 grid ran in two waves (100 us); with 4 stages two CTAs of a cluster
+//    share an SM and the grid is resident at once (67 us).
+// FTG_GEMM_STAGES=<n> / ftg_gemm_tc_set_stages force a depth (experiments).
+int g_forced_stages = -1;
+int choose_stages(long long ctas, int kblocks_per_cta, int cluster_size) {
+  if (g_forced_stages < 0) {
+    const char* e = getenv("FTG_GEMM_STAGES");
+    g_forced_stages = e ? atoi(e) : 0;
+  }
+  const int forced = g_forced_stages;
+  int s = MAX_STAGES;
+  if (forced >= 2 && forced <= MAX_STAGES) s = forced;
+  else if (ctas > 148) s = 4;
+  else if (cluster_size >= 8 && ctas > 96) s = 4;
+  if (s > kblocks_per_cta) s = kblocks_per_cta;
+  return s < 2 ? 2 : s;
 }
 
 template <bool A_MN, bool B_MN, int EPI>
@@ -456,14 +499,19 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return (int)e;
     attr_done = true;
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
+  const int stages = choose_stages((long long)grid.x * grid.y * grid.z, (ftg_cdiv(p.K, BK) + split_k - 1) / split_k,
+                                   cluster_mode ? split_k : 1);
   ++g_ftg_launch_count;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = SMEM_BYTES;
+  cfg.dynamicSmemBytes = smem_bytes(stages);
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
@@ -481,7 +529,8 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI>, ma, mb, p, split_k, ws, ctr, vec_ok, cluster_mode);
+  return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI>, ma, mb, p, split_k, ws, ctr, vec_ok, cluster_mode,
+                                 stages);
 }
 
 template <bool A_MN, bool B_MN>
@@ -539,6 +588,12 @@ extern "C" int ftg_gemm_tc_choose_split(int M, int N, int K) {
 
 // Cluster split-K factor: largest power of two <= 8 that keeps >= 2 k-blocks per CTA and the
 // grid within one wave of 148 SMs.
+// Force the ring depth of subsequent launches (2..6; 0 = automatic).  Tuning / tests only.
+extern "C" int ftg_gemm_tc_set_stages(int stages) {
+  g_forced_stages = (stages >= 2 && stages <= MAX_STAGES) ? stages : 0;
+  return 0;
+}
+
 extern "C" int ftg_gemm_tc_choose_cluster_split(int M, int N, int K) {
   int tiles = ftg_gemm_tc_num_tiles(M, N);
   int nkb = ftg_cdiv(K, BK);

@@ -224,6 +224,11 @@ def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None
     return out
 
 
+def set_gemm_stages(stages: int):
+    """Force the tcgen05 GEMM's TMA ring depth (2..6); 0 restores the automatic policy."""
+    lib.ftg_gemm_tc_set_stages(int(stages))
+
+
 def rowdot(a, w, bias, out, rowscale=None, loss_out=None):
     pa, lda = _m(a)
     if loss_out is not None:

@@ -69,6 +69,8 @@ const char* ftg_last_error_message(void);
 int ftg_gemm_tc_choose_split(int M, int N, int K);
 /* With workspace == NULL and split_k in {2,4,8} the split_k CTAs of a tile form a thread-block
  * cluster and reduce their partial tiles through distributed shared memory (no scratch). */
+/* Force the TMA ring depth of subsequent tcgen05 GEMM launches (2..6; 0 = automatic policy). */
+int ftg_gemm_tc_set_stages(int stages);
 int ftg_gemm_tc_choose_cluster_split(int M, int N, int K);
 long long ftg_gemm_tc_workspace_bytes(int M, int N, int split_k);
 int ftg_gemm_tc_num_tiles(int M, int N);
