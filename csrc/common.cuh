@@ -3,11 +3,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <math.h>
+#include <atomic>
 
 #define FTG_ERR_UNSUPPORTED 1000
 #define FTG_ERR_SCRATCH_TOO_SMALL 1001
 
-extern int g_ftg_launch_count;   // defined in elementwise.cu
+extern std::atomic<long long> g_ftg_launch_count;   // defined in elementwise.cu (RPC handler threads launch concurrently)
 
 #define FTG_LAUNCH_CHECK()                         \
   do {                                             \

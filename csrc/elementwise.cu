@@ -4,7 +4,7 @@
 #include "common.cuh"
 #include <cstdlib>
 
-int g_ftg_launch_count = 0;
+std::atomic<long long> g_ftg_launch_count{0};
 int g_ftg_pdl = [] {
   const char* e = getenv("FEDTGAN_PDL");
   return (e && e[0] == '0') ? 0 : 1;
@@ -12,7 +12,7 @@ int g_ftg_pdl = [] {
 extern "C" void ftg_set_pdl(int on) { g_ftg_pdl = on ? 1 : 0; }
 
 extern "C" const char* ftg_version(void) { return "fedtgan_b200 0.1.0 (sm_100a)"; }
-extern "C" int ftg_last_launch_count(void) { return g_ftg_launch_count; }
+extern "C" long long ftg_last_launch_count(void) { return g_ftg_launch_count.load(); }
 
 // ------------------------------------------------------------------ rng tick
 __global__ void k_tick(int64_t* state) {

@@ -495,14 +495,18 @@ template <bool A_MN, bool B_MN, int EPI>
 int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
                int vec_ok, cudaStream_t stream) {
   const int cluster_mode = (ws == nullptr && split_k > 1) ? 1 : 0;   // no workspace given: reduce through DSMEM
-  static bool attr_done = false;
-  if (!attr_done) {
+  // function attributes are per device: one flag per (instantiation, device)
+  static std::atomic<bool> attr_done_dev[64];
+  int dev_id = 0;
+  if (cudaGetDevice(&dev_id) != cudaSuccess || dev_id < 0 || dev_id >= 64) return FTG_ERR_UNSUPPORTED;
+  std::atomic<bool>& attr_done = attr_done_dev[dev_id];
+  if (!attr_done.load(std::memory_order_acquire)) {
     cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributePreferredSharedMemoryCarveout,
                              cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return (int)e;
-    attr_done = true;
+    attr_done.store(true, std::memory_order_release);
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
   const int stages = choose_stages((long long)grid.x * grid.y * grid.z, (ftg_cdiv(p.K, BK) + split_k - 1) / split_k,

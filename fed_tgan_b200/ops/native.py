@@ -99,7 +99,7 @@ _symm_open = _sig("ftg_symm_open", [C.c_char_p, C.POINTER(_vp)])
 _symm_close = _sig("ftg_symm_close", [_vp])
 _stats = _sig("ftg_stats_to_weights", [_vp, _i, _i, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp])
 _vbgmm = _sig("ftg_vbgmm_fit", [_vp, _i, _i, _vp, _i, C.c_double, _i, C.c_double, C.c_double, _i, _vp, _vp, _vp])
-_launch_count = _sig("ftg_last_launch_count", [])
+_launch_count = _sig("ftg_last_launch_count", [], _ll)
 lib.ftg_version.restype = C.c_char_p
 
 
@@ -174,6 +174,9 @@ def preallocate_scratch(device):
 def _gemm_args(a, b, out, a_t, b_t, bias, act, mask_in, mask_out, u, rng, stream, accumulate, alpha, slope, p):
     M, N = out.shape
     K = a.shape[0] if a_t else a.shape[1]
+    if out.device.index != torch.cuda.current_device():
+        # launches go to the *current* device's stream: a tensor of another GPU would be dereferenced there
+        raise NativeError(f"tensor on cuda:{out.device.index} but current device is cuda:{torch.cuda.current_device()}")
     assert (a.shape[1] if a_t else a.shape[0]) == M, (a.shape, out.shape, a_t)
     assert (b.shape[1] if b_t else b.shape[0]) == N and (b.shape[0] if b_t else b.shape[1]) == K, (b.shape, N, K, b_t)
     g = GemmArgs()

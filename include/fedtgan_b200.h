@@ -240,7 +240,7 @@ int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* n
                   const void* const* columns, const char* const* const* str_tables, int n_threads);
 
 const char* ftg_version(void);
-int ftg_last_launch_count(void);   /* kernels launched by this library since load */
+long long ftg_last_launch_count(void);   /* kernels launched by this library since load */
 
 #ifdef __cplusplus
 }
