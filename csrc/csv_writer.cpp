@@ -1,93 +1,161 @@
 // Multi-threaded CSV writer for the per-epoch synthetic table (host code).
 // The reference writes 40 000 x 42 cells with pandas inside the timed round
-// (Server/dtds/distributed.py:586-590); here each thread formats a row range
-// with std::to_chars (shortest round-trip, like Python's repr) into its own buffer.
+// (Server/dtds/distributed.py:586-590).  At 8 clients a federated round takes ~4 ms, so
+// the federator has to emit ~270 CSVs per second: the writer is built for CPU time per file.
+//  * every thread formats a row range straight into its slice of one worst-case-sized buffer
+//    (pointer bumps, no per-cell capacity checks or allocations);
+//  * the buffer belongs to the calling thread and is reused by its next call (the federator's
+//    writer pool has a few long-lived threads), so steady state takes no page faults;
+//  * category strings are quoted and measured once per call, a cell is then one memcpy;
+//  * floats use std::to_chars (shortest string that round-trips, like Python's repr), with an
+//    integer fast path for integral values (counts, ages, ... written as "123.0").
+#include <algorithm>
 #include <charconv>
+#include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <deque>
 #include <string>
 #include <thread>
 #include <vector>
-#include <cstdint>
-#include <cmath>
+
+namespace {
+
+struct StrEntry { const char* p; uint32_t len; };
+
+inline bool needs_quote(const char* s) {
+  for (const char* p = s; *p; ++p)
+    if (*p == ',' || *p == '"' || *p == '\n' || *p == '\r') return true;
+  return false;
+}
+
+void quote_into(std::string& out, const char* s) {
+  if (!needs_quote(s)) { out.append(s); return; }
+  out.push_back('"');
+  for (const char* p = s; *p; ++p) { if (*p == '"') out.push_back('"'); out.push_back(*p); }
+  out.push_back('"');
+}
+
+// integral |v| < 2^24 (float) / 2^53 (double): digits + ".0"; returns nullptr when not applicable
+template <typename T>
+inline char* put_integral(char* o, T v, T limit) {
+  if (!(v > -limit && v < limit)) return nullptr;
+  const long long i = (long long)v;
+  if ((T)i != v) return nullptr;
+  if (i == 0 && std::signbit(v)) { std::memcpy(o, "-0.0", 4); return o + 4; }
+  auto res = std::to_chars(o, o + 24, i);
+  res.ptr[0] = '.'; res.ptr[1] = '0';
+  return res.ptr + 2;
+}
+
+template <typename T>
+inline char* put_real(char* o, T v, T int_limit) {
+  if (std::isnan(v)) return o;                               // pandas writes NaN as an empty cell
+  if (std::isinf(v)) { const char* s = v > 0 ? "inf" : "-inf"; size_t n = std::strlen(s); std::memcpy(o, s, n); return o + n; }
+  if (char* e = put_integral<T>(o, v, int_limit)) return e;
+  auto res = std::to_chars(o, o + 40, v);
+  bool plain = true;
+  for (char* p = o; p < res.ptr; ++p)
+    if (*p == '.' || *p == 'e') { plain = false; break; }
+  if (plain) { res.ptr[0] = '.'; res.ptr[1] = '0'; return res.ptr + 2; }   // keep float-ness (repr style)
+  return res.ptr;
+}
+
+}  // namespace
 
 extern "C" {
 
 // kinds: 0 = float64 column, 1 = float32 column, 2 = int64 column, 3 = int32 codes into
-// str_tables[c] (NULL-terminated array of C strings is not required; codes index directly)
+// str_tables[c] (codes index the table directly; its length is taken from the largest code)
 int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
                   const void* const* columns, const char* const* const* str_tables, int n_threads) {
+  if (n_rows < 0 || n_cols <= 0) return -2;
   if (n_threads < 1) n_threads = 1;
   if (n_threads > 64) n_threads = 64;
-  std::vector<std::string> bufs(n_threads);
-  auto needs_quote = [](const char* s) {
-    for (const char* p = s; *p; ++p)
-      if (*p == ',' || *p == '"' || *p == '\n' || *p == '\r') return true;
-    return false;
-  };
-  auto put_str = [&](std::string& out, const char* s) {
-    if (!needs_quote(s)) { out.append(s); return; }
-    out.push_back('"');
-    for (const char* p = s; *p; ++p) { if (*p == '"') out.push_back('"'); out.push_back(*p); }
-    out.push_back('"');
-  };
-  auto put_float = [](std::string& out, float v) {
-    if (std::isnan(v)) return;
-    if (std::isinf(v)) { out.append(v > 0 ? "inf" : "-inf"); return; }
-    char tmp[24];
-    auto res = std::to_chars(tmp, tmp + sizeof(tmp), v);      // shortest string that round-trips the float32
-    bool plain = true;
-    for (char* p = tmp; p < res.ptr; ++p)
-      if (*p == '.' || *p == 'e') { plain = false; break; }
-    out.append(tmp, res.ptr - tmp);
-    if (plain) out.append(".0");
-  };
-  auto put_double = [](std::string& out, double v) {
-    if (std::isnan(v)) return;                        // pandas writes NaN as empty
-    if (std::isinf(v)) { out.append(v > 0 ? "inf" : "-inf"); return; }
-    char tmp[40];
-    auto res = std::to_chars(tmp, tmp + sizeof(tmp), v);
-    bool plain = true;
-    for (char* p = tmp; p < res.ptr; ++p)
-      if (*p == '.' || *p == 'e' || *p == 'n' || *p == 'i') { plain = false; break; }
-    out.append(tmp, res.ptr - tmp);
-    if (plain) out.append(".0");                      // keep float-ness (repr style)
-  };
+  if (n_threads > n_rows) n_threads = n_rows > 0 ? n_rows : 1;
+
+  // ---- per-column preparation: quoted category strings, worst-case cell width
+  std::vector<std::vector<StrEntry>> tables(n_cols);
+  std::deque<std::string> quoted_store;                      // owns the strings that needed quoting (stable addresses)
+  size_t row_bytes = 1;                                      // '\n'
+  for (int c = 0; c < n_cols; ++c) {
+    size_t w = 0;
+    switch (kinds[c]) {
+      case 0: w = 26; break;                                 // "-2.2250738585072014e-308" is 24 characters
+      case 1: w = 16; break;                                 // "-1.17549435e-38" is 15
+      case 2: w = 21; break;
+      default: {
+        const int32_t* codes = static_cast<const int32_t*>(columns[c]);
+        int32_t mx = -1;
+        for (int r = 0; r < n_rows; ++r) {
+          if (codes[r] < 0) return -3;
+          if (codes[r] > mx) mx = codes[r];
+        }
+        tables[c].resize((size_t)(mx + 1));
+        for (int32_t k = 0; k <= mx; ++k) {
+          const char* s = str_tables[c][k];
+          if (needs_quote(s)) {
+            quoted_store.emplace_back();
+            quote_into(quoted_store.back(), s);
+            tables[c][k] = {quoted_store.back().data(), (uint32_t)quoted_store.back().size()};
+          } else {
+            tables[c][k] = {s, (uint32_t)std::strlen(s)};
+          }
+          if (tables[c][k].len > w) w = tables[c][k].len;
+        }
+        break;
+      }
+    }
+    row_bytes += w + 1;                                      // cell + ','
+  }
+
+  // ---- one worst-case-sized buffer per calling thread, reused across calls
+  static thread_local std::vector<char> buffer;
+  const size_t rows_per = ((size_t)n_rows + n_threads - 1) / n_threads;
+  const size_t slice = rows_per * row_bytes;
+  if (buffer.size() < slice * n_threads) buffer.resize(slice * n_threads);
+  char* const base = buffer.data();
+  std::vector<size_t> used(n_threads, 0);
+
   auto work = [&](int t) {
-    long long r0 = (long long)n_rows * t / n_threads, r1 = (long long)n_rows * (t + 1) / n_threads;
-    std::string& out = bufs[t];
-    out.reserve((size_t)(r1 - r0) * n_cols * 14);
+    const long long r0 = (long long)rows_per * t;
+    const long long r1 = std::min<long long>(n_rows, r0 + (long long)rows_per);
+    char* o = base + slice * t;
     for (long long r = r0; r < r1; ++r) {
       for (int c = 0; c < n_cols; ++c) {
-        if (c) out.push_back(',');
+        if (c) *o++ = ',';
         switch (kinds[c]) {
-          case 0: put_double(out, static_cast<const double*>(columns[c])[r]); break;
-          case 1: put_float(out, static_cast<const float*>(columns[c])[r]); break;
-          case 2: {
-            char tmp[24];
-            auto res = std::to_chars(tmp, tmp + sizeof(tmp), static_cast<const int64_t*>(columns[c])[r]);
-            out.append(tmp, res.ptr - tmp);
+          case 0: o = put_real<double>(o, static_cast<const double*>(columns[c])[r], 9007199254740992.0); break;
+          case 1: o = put_real<float>(o, static_cast<const float*>(columns[c])[r], 16777216.0f); break;
+          case 2: o = std::to_chars(o, o + 24, static_cast<const int64_t*>(columns[c])[r]).ptr; break;
+          default: {
+            const StrEntry& e = tables[c][static_cast<const int32_t*>(columns[c])[r]];
+            std::memcpy(o, e.p, e.len);
+            o += e.len;
             break;
           }
-          default: put_str(out, str_tables[c][static_cast<const int32_t*>(columns[c])[r]]); break;
         }
       }
-      out.push_back('\n');
+      *o++ = '\n';
     }
+    used[t] = (size_t)(o - (base + slice * t));
   };
   std::vector<std::thread> pool;
   for (int t = 1; t < n_threads; ++t) pool.emplace_back(work, t);
   work(0);
   for (auto& th : pool) th.join();
+
   FILE* f = std::fopen(path, "wb");
   if (!f) return -1;
   std::string header;
-  for (int c = 0; c < n_cols; ++c) { if (c) header.push_back(','); put_str(header, names[c]); }
+  for (int c = 0; c < n_cols; ++c) { if (c) header.push_back(','); quote_into(header, names[c]); }
   header.push_back('\n');
-  std::fwrite(header.data(), 1, header.size(), f);
-  for (auto& b : bufs) std::fwrite(b.data(), 1, b.size(), f);
-  std::fclose(f);
-  return 0;
+  bool ok = std::fwrite(header.data(), 1, header.size(), f) == header.size();
+  for (int t = 0; t < n_threads && ok; ++t) ok = std::fwrite(base + slice * t, 1, used[t], f) == used[t];
+  ok = (std::fclose(f) == 0) && ok;
+  if (buffer.size() > ((size_t)256 << 20)) std::vector<char>().swap(buffer);   // do not pin huge tables
+  return ok ? 0 : -4;
 }
 
 }  // extern "C"

@@ -234,3 +234,30 @@ def test_native_csv_writer_matches_pandas(tmp_path):
     assert list(back["cat"]) == [cols[1][1][c] for c in cols[1][0]]
     assert np.array_equal(back["i"].to_numpy(), cols[2])
     assert np.allclose(back["tiny"].to_numpy(), cols[3], rtol=1e-15, atol=0)
+
+
+def test_native_csv_writer_special_values(tmp_path):
+    """Integral fast path, signed zero, inf / NaN, quoting, more threads than rows, repeated calls
+    on the same thread (the writer reuses its buffer)."""
+    from fed_tgan_b200.ops import hostlib
+
+    if not hostlib.available():
+        import pytest
+        pytest.skip("native library not built")
+    f32 = np.array([0.0, -0.0, 1.0, -5.0, 16777215.0, 16777216.0, 3e9, 1e-30, 0.1, np.inf, -np.inf, np.nan], np.float32)
+    f64 = np.array([1e22, -0.0, 123456789012.0, 0.1, 2.0 ** 53, -(2.0 ** 53) + 1, 5e-324, 1.5, -2.0, np.inf, np.nan, 7.0])
+    i64 = np.arange(12, dtype=np.int64) * -(10 ** 11)
+    codes = (np.arange(12, dtype=np.int32) % 3, ['pl"ain', "with,comma", "x"])
+    for n_threads in (1, 5, 64):
+        for rep in range(2):
+            path = str(tmp_path / f"s{n_threads}.csv")
+            hostlib.write_csv(path, ['a "q"', "b", "c", "d"], [f32, f64, i64, codes], n_threads=n_threads)
+            back = pd.read_csv(path, float_precision="round_trip")
+            assert list(back.columns) == ['a "q"', "b", "c", "d"] and len(back) == 12
+            assert np.array_equal(back['a "q"'].to_numpy(np.float32), f32, equal_nan=True)
+            assert np.array_equal(np.signbit(back['a "q"'].to_numpy()[:2]), [False, True])
+            assert np.array_equal(back["b"].to_numpy(), f64, equal_nan=True)
+            assert np.array_equal(back["c"].to_numpy(), i64)
+            assert list(back["d"]) == [codes[1][c] for c in codes[0]]
+    text = open(tmp_path / "s1.csv").read().splitlines()
+    assert text[3].startswith("1.0,") and text[4].startswith("-5.0,")      # integral floats keep their ".0"
