@@ -261,3 +261,27 @@ def test_native_csv_writer_special_values(tmp_path):
             assert list(back["d"]) == [codes[1][c] for c in codes[0]]
     text = open(tmp_path / "s1.csv").read().splitlines()
     assert text[3].startswith("1.0,") and text[4].startswith("-5.0,")      # integral floats keep their ".0"
+
+
+def test_gradflow_and_local_entry(tmp_path):
+    """P14 (gradient-flow diagnostics, headless) and P24 (stand-alone ``local`` entry point)."""
+    from helpers import small_setup
+    from fed_tgan_b200 import local
+    from fed_tgan_b200.utils import gradflow
+
+    _, _, _, eng = small_setup()
+    eng.train(2)
+    gradflow.update_grad_flow(eng.G, "G")
+    gradflow.update_grad_flow(eng.D, "D")
+    out = gradflow.plot_grad_flow(str(tmp_path / "gf"))
+    assert os.path.exists(out) and os.path.getsize(out) > 0
+    assert gradflow.layers["D"][0] == "seq.0.weight" and len(gradflow.ave_grads["G"][-1]) == len(gradflow.layers["G"])
+
+    rng = np.random.default_rng(0)
+    df = pd.DataFrame({"x": rng.normal(size=300), "k": rng.choice(["a", "b", "c"], 300), "y": rng.exponential(size=300)})
+    df.to_csv(tmp_path / "toy.csv", index=False)
+    synth = local.main(["-dataset", str(tmp_path / "toy.csv"), "-categorical_list", "k", "-epochs", "1", "-report",
+                        "-out", str(tmp_path / "toy_syn.csv")])
+    back = pd.read_csv(tmp_path / "toy_syn.csv")
+    assert list(back.columns) == ["x", "k", "y"] and len(back) == 1000 and set(back["k"]) <= {"a", "b", "c"}
+    assert synth is not None
