@@ -417,6 +417,162 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   }
 }
 
+// ------------------------------------------------------------------ persistent variant
+// One CTA per SM walks the output tiles (m fastest, so neighbouring CTAs share a B panel in L2).  The
+// TMA ring runs ahead across tile boundaries, the accumulator is double-buffered in TMEM (2 x 64
+// columns): while the epilogue warps drain tile i from one half, the MMA issuer already fills the other
+// half with tile i+1, and barrier init / TMEM allocation / descriptor prefetch are paid once per CTA
+// instead of once per tile.  No split-K (multi-wave grids only).  The staged epilogue tile has its own
+// shared-memory area here because the operand ring never goes idle.
+// EXPERIMENTAL: opt-in (FTG_GEMM_PERSISTENT=1 / ftg_gemm_tc_set_persistent); the default launch path
+// does not use it.
+constexpr int PERSIST_STAGES = 5;
+constexpr int PERSIST_STAGE_TILE_BYTES = BM * SLD * 4;                       // 34 816 B
+constexpr int PERSIST_SMEM_BYTES = PERSIST_STAGES * STAGE_BYTES + PERSIST_STAGE_TILE_BYTES + 1024 + 256;
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+k_gemm_tc_persist(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                  const ftg_gemm_args p, int vec_ok_i, int tiles_m, int tiles_n) {
+  constexpr int S = PERSIST_STAGES;
+  const bool vec_ok = vec_ok_i != 0;
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  unsigned char* gen_base = smem_raw + (base - raw);
+  float* stage = reinterpret_cast<float*>(gen_base + S * STAGE_BYTES);         // dedicated epilogue staging tile
+  const uint32_t bars = base + S * STAGE_BYTES + PERSIST_STAGE_TILE_BYTES;
+  // full[S], empty[S], tmem_full[2], tmem_empty[2], tmem_slot
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (S + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * S + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * S + 2 + a); };
+  volatile uint32_t* tmem_slot =
+      reinterpret_cast<volatile uint32_t*>(gen_base + S * STAGE_BYTES + PERSIST_STAGE_TILE_BYTES + 8 * (2 * S + 4));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nkb = (p.K + BK - 1) / BK;
+  const int n_tiles = tiles_m * tiles_n;
+
+  asm volatile("griddepcontrol.launch_dependents;");
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }   // 4 epilogue warps
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32((const void*)tmem_slot)), "r"(2 * TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+
+  if (warp == 0 && lane == 0) {
+    // ------------------------------------------------------------ TMA producer (runs ahead over tiles)
+    int s = 0;
+    uint32_t phase = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      const int m0 = (t % tiles_m) * BM, n0 = (t / tiles_m) * BN;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(empty_bar(s), phase ^ 1u);
+        const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
+        mbar_expect_tx(full_bar(s), STAGE_BYTES);
+        const int k = kb * BK;
+        if (A_MN) {
+#pragma unroll
+          for (int c = 0; c < BM / 32; ++c) tma_load_2d(sa + c * (BK * 128), &map_a, full_bar(s), m0 + c * 32, k);
+        } else {
+          tma_load_2d(sa, &map_a, full_bar(s), k, m0);
+        }
+        if (B_MN) {
+#pragma unroll
+          for (int c = 0; c < BN / 32; ++c) tma_load_2d(sb + c * (BK * 128), &map_b, full_bar(s), n0 + c * 32, k);
+        } else {
+          tma_load_2d(sb, &map_b, full_bar(s), k, n0);
+        }
+        if (++s == S) { s = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // -------------------------------------------------------------- MMA issuer
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    int s = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
+      mbar_wait(tempty_bar(acc), acc_phase ^ 1u);            // epilogue has drained this accumulator half
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TMEM_COLS);
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(full_bar(s), phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
+#pragma unroll
+        for (int ks = 0; ks < BK / 8; ++ks) {
+          uint64_t ad = A_MN ? make_desc(sa + ks * 1024, BK * 128, 512, 1) : make_desc(sa + ks * 32, 16, 1024, 2);
+          uint64_t bd = B_MN ? make_desc(sb + ks * 1024, BK * 128, 512, 1) : make_desc(sb + ks * 32, 16, 1024, 2);
+          umma_tf32(d_tmem, ad, bd, idesc, (kb > 0 || ks > 0) ? 1u : 0u);
+        }
+        umma_commit(empty_bar(s));
+        if (++s == S) { s = 0; phase ^= 1u; }
+      }
+      umma_commit(tfull_bar(acc));
+    }
+  } else if (warp >= 2) {
+    // ---------------------------------------------------------------- epilogue warps
+    const int q = warp & 3;
+    const int row_in_tile = q * 32 + lane;
+    const int et = threadIdx.x - 64;
+    int it = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+      const int m0 = (t % tiles_m) * BM, n0 = (t / tiles_m) * BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      uint32_t r[64];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * TMEM_COLS);
+      tmem_ld32(taddr, r);
+      tmem_ld32(taddr + 32, r + 32);
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      // the accumulator half is in registers: hand it back to the MMA issuer before the slow part
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      asm volatile("bar.sync 1, 128;" ::: "memory");           // previous tile's staged data fully consumed
+      {
+        float4* myrow = reinterpret_cast<float4*>(stage + row_in_tile * SLD);
+#pragma unroll
+        for (int j = 0; j < BN / 4; ++j)
+          myrow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                 __uint_as_float(r[4 * j + 3]));
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");           // whole tile staged
+      epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0, 0, CHUNKS);
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * TMEM_COLS) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -491,6 +647,16 @@ int choose_stages(long long ctas, int kblocks_per_cta, int cluster_size) {
   return s < 2 ? 2 : s;
 }
 
+// Persistent-tile variant: opt-in (experimental).
+int g_persistent = -1;
+bool use_persistent() {
+  if (g_persistent < 0) {
+    const char* e = getenv("FTG_GEMM_PERSISTENT");
+    g_persistent = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return g_persistent == 1;
+}
+
 template <bool A_MN, bool B_MN, int EPI>
 int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
                int vec_ok, cudaStream_t stream) {
@@ -509,6 +675,27 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
     attr_done.store(true, std::memory_order_release);
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
+  if (use_persistent() && split_k == 1 && (long long)grid.x * grid.y > 148) {
+    static std::atomic<bool> pattr_done_dev[64];
+    if (!pattr_done_dev[dev_id].load(std::memory_order_acquire)) {
+      cudaError_t e = cudaFuncSetAttribute(k_gemm_tc_persist<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           PERSIST_SMEM_BYTES);
+      if (e != cudaSuccess) return (int)e;
+      pattr_done_dev[dev_id].store(true, std::memory_order_release);
+    }
+    ++g_ftg_launch_count;
+    cudaLaunchConfig_t pc = {};
+    pc.gridDim = dim3(148);
+    pc.blockDim = dim3(NUM_THREADS);
+    pc.dynamicSmemBytes = PERSIST_SMEM_BYTES;
+    pc.stream = stream;
+    cudaLaunchAttribute pattr[1];
+    pattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pattr[0].val.programmaticStreamSerializationAllowed = 1;
+    pc.attrs = pattr;
+    pc.numAttrs = g_ftg_pdl ? 1 : 0;
+    return (int)cudaLaunchKernelEx(&pc, k_gemm_tc_persist<A_MN, B_MN, EPI>, ma, mb, p, vec_ok, (int)grid.y, (int)grid.x);
+  }
   const int stages = choose_stages((long long)grid.x * grid.y * grid.z, (ftg_cdiv(p.K, BK) + split_k - 1) / split_k,
                                    cluster_mode ? split_k : 1);
   ++g_ftg_launch_count;
@@ -595,6 +782,12 @@ extern "C" int ftg_gemm_tc_choose_split(int M, int N, int K) {
 // Force the ring depth of subsequent launches (2..6; 0 = automatic).  Tuning / tests only.
 extern "C" int ftg_gemm_tc_set_stages(int stages) {
   g_forced_stages = (stages >= 2 && stages <= MAX_STAGES) ? stages : 0;
+  return 0;
+}
+
+// 1: multi-wave unsplit GEMMs use the persistent double-buffered-TMEM kernel (experimental); 0: never.
+extern "C" int ftg_gemm_tc_set_persistent(int on) {
+  g_persistent = on ? 1 : 0;
   return 0;
 }
 

@@ -232,6 +232,11 @@ def set_gemm_stages(stages: int):
     lib.ftg_gemm_tc_set_stages(int(stages))
 
 
+def set_gemm_persistent(on: bool):
+    """Experimental: multi-wave unsplit GEMMs through the persistent double-buffered-TMEM kernel."""
+    lib.ftg_gemm_tc_set_persistent(int(bool(on)))
+
+
 def rowdot(a, w, bias, out, rowscale=None, loss_out=None):
     pa, lda = _m(a)
     if loss_out is not None:

@@ -71,6 +71,9 @@ int ftg_gemm_tc_choose_split(int M, int N, int K);
  * cluster and reduce their partial tiles through distributed shared memory (no scratch). */
 /* Force the TMA ring depth of subsequent tcgen05 GEMM launches (2..6; 0 = automatic policy). */
 int ftg_gemm_tc_set_stages(int stages);
+/* Experimental: route multi-wave, unsplit tcgen05 GEMMs through the persistent kernel (one CTA per SM,
+ * double-buffered TMEM accumulator).  Off by default. */
+int ftg_gemm_tc_set_persistent(int on);
 int ftg_gemm_tc_choose_cluster_split(int M, int N, int K);
 long long ftg_gemm_tc_workspace_bytes(int M, int N, int split_k);
 int ftg_gemm_tc_num_tiles(int M, int N);
