@@ -497,3 +497,27 @@ def test_stats_kernel_near_identical_histograms(N):
     jr = W.categorical_similarity(cv)
     assert np.allclose(jsd.cpu().numpy(), jr, atol=2e-3), (jsd.cpu().numpy(), jr)
     assert np.allclose(wt.cpu().numpy(), W.final_weights(jr, np.zeros((world, 0)), rows), atol=1e-3)
+
+
+def test_gemm_persistent_variant_is_bitwise_identical(N):
+    """Opt-in persistent kernel (one CTA per SM, double-buffered TMEM accumulator): same MMAs in the same
+    order per tile, so multi-wave GEMMs must reproduce the default kernel bit for bit."""
+    torch.manual_seed(0)
+    for (M, Nn, K, a_t, b_t) in [(1624, 3700, 500, True, True), (8192, 256, 252, False, False),
+                                 (52, 31480, 1024, False, True)]:
+        a = torch.randn((K, M) if a_t else (M, K), device=dev())
+        b = torch.randn((K, Nn) if b_t else (Nn, K), device=dev())
+        bias = torch.randn(Nn, device=dev())
+        outs = []
+        try:
+            for mode in (False, True):
+                N.set_gemm_persistent(mode)
+                out = torch.full((M, Nn), float("nan"), device=dev())
+                N.linear(a, b, out, a_t=a_t, b_t=b_t, bias=bias, precision="tf32")
+                outs.append(out)
+        finally:
+            N.set_gemm_persistent(False)
+        torch.cuda.synchronize()
+        assert torch.equal(outs[0], outs[1]), (M, Nn, K)
+        ref = (a.t() if a_t else a) @ (b if b_t else b.t()) + bias
+        assert ((outs[1] - ref).abs().max() / ref.abs().max()).item() < 5e-3
