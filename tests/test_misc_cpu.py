@@ -285,3 +285,26 @@ def test_gradflow_and_local_entry(tmp_path):
     back = pd.read_csv(tmp_path / "toy_syn.csv")
     assert list(back.columns) == ["x", "k", "y"] and len(back) == 1000 and set(back["k"]) <= {"a", "b", "c"}
     assert synth is not None
+
+
+def test_gemm_host_side_policies():
+    """Host-side launch policy helpers of the tcgen05 GEMM (no GPU needed: plain C functions)."""
+    import ctypes as C
+
+    from fed_tgan_b200.ops import build, hostlib
+
+    if not hostlib.available():
+        import pytest
+        pytest.skip("native library not built")
+    lib = C.CDLL(build.LIB)
+    tiles = lib.ftg_gemm_tc_num_tiles
+    split = lib.ftg_gemm_tc_choose_cluster_split
+    assert tiles(500, 256) == 4 * 4 and tiles(50, 1024) == 16 and tiles(129, 65) == 2 * 2
+    for (M, N, K) in [(150, 256, 2500), (500, 256, 250), (50, 1024, 31480), (8192, 256, 250), (500, 128, 764)]:
+        s = split(M, N, K)
+        assert s in (1, 2, 4, 8)                                   # power-of-two cluster along K
+        assert s == 1 or tiles(M, N) * s <= 148                    # split-K never spills past one wave
+        assert s == 1 or (K + 31) // 32 // s >= 2                  # at least two k-blocks per CTA
+    assert split(8192, 256, 250) == 1 and split(50, 1024, 31480) == 8
+    lib.ftg_gemm_tc_workspace_bytes.restype = C.c_longlong
+    assert lib.ftg_gemm_tc_workspace_bytes(150, 256, 4) == 4 * tiles(150, 256) * 128 * 64 * 4
