@@ -114,7 +114,7 @@ int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* n
   static thread_local std::vector<char> buffer;
   const size_t rows_per = ((size_t)n_rows + n_threads - 1) / n_threads;
   const size_t slice = rows_per * row_bytes;
-  if (buffer.size() < slice * n_threads) buffer.resize(slice * n_threads);
+  if (buffer.size() < slice * n_threads + 64) buffer.resize(slice * n_threads + 64);   // +64: to_chars end bounds stay inside
   char* const base = buffer.data();
   std::vector<size_t> used(n_threads, 0);
 
