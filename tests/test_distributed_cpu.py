@@ -74,3 +74,30 @@ def test_spmd_gloo_two_ranks(tmp_path):
     for i in range(2):
         df = pd.read_csv(tmp_path / "Adult_result" / f"Adult_synthesis_epoch_{i}.csv")
         assert list(df.columns) == schema.columns and len(df) == 150
+
+
+def test_spmd_gloo_checkpoint_resume(tmp_path):
+    """SPMD mode: a run stopped after epoch 0 resumes from the checkpoint (states all-gathered to rank 0 for
+    saving, broadcast back on load) and only trains the missing epoch."""
+    schema = get_schema("adult", rows=700)
+    make_table(schema, seed=4).to_csv(tmp_path / "Adult_train.csv", index=False)
+
+    def launch(epochs, extra):
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+               "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), "-m", "dtds.distributed", "--spmd",
+               "--cpu", "-epochs", str(epochs), "-datapath", str(tmp_path / "Adult_train.csv"), "--out_dir", str(tmp_path),
+               "-selected_variables", ",".join(schema.columns), "-categorical_list", ",".join(schema.categorical),
+               "-nonnegative_list", "", "-target_column", schema.target, "--vgm_backend", "vb", "--batch_size", "100",
+               "--sample_rows", "120", "--gen_dim", "16,16", "--dis_dim", "16,16", "--checkpoint_every", "1"] + extra
+        res = subprocess.run(cmd, cwd=tmp_path, env=_env(), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=600)
+        assert res.returncode == 0, res.stdout.decode(errors="replace")[-4000:]
+
+    launch(1, [])
+    ck = tmp_path / "models" / "checkpoint_Adult.pt"
+    assert ck.exists()
+    first = (tmp_path / "Adult_result" / "Adult_synthesis_epoch_0.csv").stat().st_mtime_ns
+    launch(2, ["--resume"])
+    assert (tmp_path / "Adult_result" / "Adult_synthesis_epoch_1.csv").exists()
+    assert (tmp_path / "Adult_result" / "Adult_synthesis_epoch_0.csv").stat().st_mtime_ns == first   # epoch 0 not redone
+    ts = pd.read_csv(tmp_path / "timestamp_experiment.csv", header=None)
+    assert len(ts) == 2
