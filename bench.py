@@ -114,7 +114,6 @@ def dist_env():
 
 # ------------------------------------------------------------------------ ours
 def run_ours(args):
-    import numpy as np
     import torch
     import torch.distributed as dist
 

@@ -10,7 +10,7 @@ that every layer takes, so the wide-table config (1024-wide nets) is just anothe
 
 from __future__ import annotations
 
-from dataclasses import dataclass, field, asdict
+from dataclasses import dataclass, asdict
 from typing import Tuple
 
 

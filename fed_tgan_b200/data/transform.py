@@ -18,7 +18,7 @@ import json
 import numpy as np
 import pandas as pd
 
-from .constants import CATEGORICAL, EMPTY_TOKEN
+from .constants import EMPTY_TOKEN
 from .date import Date
 
 

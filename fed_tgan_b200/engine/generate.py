@@ -11,7 +11,6 @@ categoricals); string decoding / CSV formatting stay on the host.
 
 from __future__ import annotations
 
-import numpy as np
 import torch
 
 from .. import ops

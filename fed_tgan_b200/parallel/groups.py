@@ -20,7 +20,6 @@ from __future__ import annotations
 import os
 import warnings
 
-import numpy as np
 import torch
 import torch.distributed as dist
 
