@@ -70,3 +70,32 @@ for (M, N, K, a_t, b_t) in SHAPES:
           + f" | best {best}  {rec['GBps_best']} GB/s  {rec['TFLOPs_best']} TFLOP/s", flush=True)
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 json.dump(rows, open(os.path.join(ROOT, "gpurun_out", "gemm_stage_sweep.json"), "w"), indent=1)
+
+# ---- split-K sweep for the skinny weight-streaming shapes: cluster (DSMEM) splits vs workspace splits that
+# put two CTAs on every SM.  Leading dimensions are multiples of 4 floats (tcgen05 path, never the SIMT fallback).
+SKINNY = [(50, 1024, 31480), (150, 1024, 31480), (50, 256, 2500), (150, 256, 2500)]
+srows = []
+for (M, N, K) in SKINNY:
+    A = [torch.randn(M, K, device=dev) for _ in range(3)]
+    B = [torch.randn(N, K, device=dev) for _ in range(3)]
+    out = torch.empty(M, N, device=dev)
+    ref = A[0] @ B[0].t()
+    rec = {"M": M, "N": N, "K": K, "us": {}}
+    for label, kw in [("cluster", {})] + [(f"ws{sk}", {"split_k": sk}) for sk in (4, 8, 16, 24, 32)]:
+        native.linear(A[0], B[0], out, **kw)
+        torch.cuda.synchronize()
+        err = ((out - ref).abs().max() / ref.abs().max()).item()
+        assert err < 2e-2, (M, N, K, label, err)
+        ts = []
+        for r in range(REPS):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            native.linear(A[r % 3], B[r % 3], out, **kw)
+            e.record()
+            e.synchronize()
+            ts.append(s.elapsed_time(e) * 1e3)
+        ts.sort()
+        rec["us"][label] = {"median": round(ts[len(ts) // 2], 2), "min": round(ts[0], 2)}
+    srows.append(rec)
+    print(f"M{M:5d} N{N:6d} K{K:6d} NN | " + "  ".join(f"{k}:{v['median']:7.1f}" for k, v in rec["us"].items()), flush=True)
+json.dump(srows, open(os.path.join(ROOT, "gpurun_out", "gemm_splitk_sweep.json"), "w"), indent=1)

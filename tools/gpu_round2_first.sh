@@ -11,4 +11,5 @@ for mode in 0 1; do
     echo "-- persistent=$mode $cfg rc=$?"; head -1 gpurun_out/r2_profile_p${mode}_${cfg}.log | cut -c1-400
   done
 done
+echo "== stage / split-K sweep"; timeout 120 python tools/gemm_stage_sweep.py > gpurun_out/r2_sweep.log 2>&1; echo "rc=$?"; tail -6 gpurun_out/r2_sweep.log
 echo "== bench persistent=1"; FTG_GEMM_PERSISTENT=1 timeout 200 python bench.py --steps 5 --warmup 3 > gpurun_out/r2_bench_persist.log 2>&1; echo "rc=$?"; tail -1 gpurun_out/r2_bench_persist.log | cut -c1-300
