@@ -78,6 +78,8 @@ def build_parser():
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--rpc_timeout", type=float, default=600.0)
     p.add_argument("--checkpoint_every", type=int, default=0)
+    p.add_argument("--aggregation", choices=["twoshot", "nvls"], default=None,
+                   help="SPMD aggregation kernel: P2P two-shot (default) or NVSwitch multimem reduce")
     p.add_argument("--resume", action="store_true")
     p.add_argument("--cpu", action="store_true", help="force CPU clients (gloo/RPC test config)")
     return p
@@ -174,6 +176,8 @@ def run_spmd(args):
         dist.init_process_group("nccl" if on_gpu else "gloo", rank=rank, world_size=world)
     cfg = config_from_args(args)
     device = f"cuda:{local}" if on_gpu else "cpu"
+    if getattr(args, "aggregation", None):
+        os.environ["FEDTGAN_AGGREGATION"] = args.aggregation
     client = MDGANClient(**client_kwargs(args, cfg, rank, device))
     server = MDGANServer(SpmdGroup(client), epochs=args.epochs, config=cfg, name=dataset_name(args.datapath),
                          out_dir=args.out_dir, vgm_backend=args.vgm_backend, device=device,
