@@ -77,36 +77,88 @@ def _spawn(spec, gpu, log):
             env.pop(k, None)
     fh = open(log, "w")
     return subprocess.Popen([sys.executable, os.path.join(HERE, "ref_worker.py"), json.dumps(spec)],
-                            env=env, stdout=fh, stderr=subprocess.STDOUT)
+                            env=env, stdout=fh, stderr=subprocess.STDOUT, start_new_session=True)
+
+
+def _kill(p):
+    try:
+        os.killpg(p.pid, 9)          # the worker is its own session leader (start_new_session)
+    except Exception:
+        try:
+            p.kill()
+        except Exception:
+            pass
+
+
+def _round_csvs(base):
+    d = os.path.join(base, "server", "Intrusion_result")
+    try:
+        fs = [os.path.join(d, f) for f in os.listdir(d) if f.endswith(".csv")]
+    except OSError:
+        return []
+    out = []
+    for f in fs:
+        try:
+            idx = int(os.path.splitext(f)[0].rsplit("_", 1)[1])
+            out.append((idx, os.path.getmtime(f)))
+        except Exception:
+            pass
+    return sorted(out)
 
 
 def run_reference_bench(args):
+    """Budgeted run.  The reference's round is ~30 s at N=1 on the Adult shape, so warm-up + steps can
+    exceed the driver's per-run limit.  The harness therefore watches the per-epoch CSVs the reference
+    writes (``Intrusion_result/Intrusion_synthesis_epoch_<i>.csv``, one per round, written at the same
+    point of every round): if the whole run will not fit ``FEDTGAN_REF_BUDGET_S`` (default 720 s) it
+    stops the reference at the budget and reports the rounds that did complete (period between
+    consecutive CSVs = one full round), saying so in the JSON (``truncated``, actual ``steps``).  A run
+    that fits is reported from the reference's own clock (``timestamp_experiment.csv``)."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
-    if not os.path.isdir(os.path.join(REF, "dtds")):
-        if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is not installed (see DESIGN.md)"}))
-        return
+    try:
+        sys.path.insert(0, HERE)
+        import install_ref
+
+        ok = install_ref.ensure_installed() if rank == 0 else True
+    except Exception as exc:
+        ok = False
+        why = f"installing baseline/_ref failed: {exc}"[:300]
+    else:
+        why = "baseline/_ref is not installed and /root/reference is not on this machine (run __graft_entry__.build() first)"
     sys.path.insert(0, ROOT)
     from fed_tgan_b200.data.schemas import get_schema, make_table, split_table   # data generation only
 
     schema = get_schema(args.config, rows=args.rows)
     n_clients = max(world, 1)
-    epochs = max(args.warmup, 1) + args.steps
+    warm = max(args.warmup, 1)
+    epochs = warm + args.steps
     base_port = 23000 + (os.getpid() % 2000 if world == 1 else int(os.environ.get("MASTER_PORT", "29500")) % 2000)
+    budget = float(os.environ.get("FEDTGAN_REF_BUDGET_S", "720"))
+    t_begin = time.time()
     if world > 1:
         import torch.distributed as dist
 
         dist.init_process_group("gloo", rank=rank, world_size=world)
-        box = [tempfile.mkdtemp(prefix="fedtgan_ref_") if rank == 0 else None]
+        box = [tempfile.mkdtemp(prefix="fedtgan_ref_") if rank == 0 else None, ok]
         dist.broadcast_object_list(box, src=0)
-        base = box[0]
+        base, ok = box
     else:
         base = tempfile.mkdtemp(prefix="fedtgan_ref_")
+    if not ok or not os.path.isdir(os.path.join(REF, "dtds")):
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    mode = "skewed" if args.config == "covertype" else "iid"
+    n_rows = None
     if rank == 0:
         df = make_table(schema, seed=0)
-        shards = split_table(df, n_clients, "skewed" if args.config == "covertype" else "iid", seed=0)
+        n_rows = len(df)
+        shards = split_table(df, n_clients, mode, seed=0)
+        shard_rows = [len(s) for s in shards]
         _prepare_dirs(base, schema, df, shards)
     if world > 1:
         dist.barrier()
@@ -119,42 +171,65 @@ def run_reference_bench(args):
                             os.path.join(base, "server.log")))
     procs.append(_spawn(dict(common, rank=rank + 1, cwd=os.path.join(base, f"client{rank + 1}")), local,
                         os.path.join(base, f"client{rank + 1}.log")))
-    limit = 600 + 90 * epochs                      # generous; a healthy round takes ~30 s
-    rc = []
-    for p in procs:
-        try:
-            rc.append(p.wait(timeout=max(1, limit - (time.time() - t0))))
-        except subprocess.TimeoutExpired:
-            p.kill()
-            rc.append(-9)
+    stop_file = os.path.join(base, "STOP")
+    truncated = False
+    while any(p.poll() is None for p in procs):
+        time.sleep(0.5)
+        if rank == 0 and time.time() - t_begin > budget and not os.path.exists(stop_file):
+            open(stop_file, "w").close()
+        if os.path.exists(stop_file):
+            truncated = True
+            for p in procs:
+                if p.poll() is None:
+                    _kill(p)
+    rc = [p.wait() for p in procs]
     wall = time.time() - t0
     if world > 1:
         dist.barrier()
     if rank == 0:
         out = {"impl": "reference", "metric": "federated_epochs_per_sec", "unit": "federated_epochs/s",
-               "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 1), "higher_is_better": True,
-               "scaling": "strong", "dtype": "fp32", "data": "synthetic"}
+               "n_gpus": world, "steps": args.steps, "warmup": warm, "higher_is_better": True,
+               "scaling": "strong", "dtype": "fp32", "data": "synthetic", "gpu_launches": None}
         ts_path = os.path.join(base, "server", "timestamp_experiment.csv")
-        if any(rc) or not os.path.exists(ts_path):
+        times, how = None, None
+        if not truncated and not any(rc) and os.path.exists(ts_path):
+            times = [float(x) for x in open(ts_path).read().split()]
+            timed = times[-args.steps:]
+            how = "reference's own per-round wall clock (timestamp_experiment.csv), warm-up rounds dropped"
+        elif truncated:
+            marks = _round_csvs(base)
+            periods = [b[1] - a[1] for a, b in zip(marks, marks[1:]) if b[0] == a[0] + 1]
+            # period k covers round k+1 (CSV k -> CSV k+1); round 0 is never inside a period
+            drop = max(0, min(warm - 1, len(periods) - 1))
+            timed = periods[drop:]
+            times = periods
+            if timed:
+                out.update({"truncated": True, "requested_steps": args.steps, "requested_warmup": warm,
+                            "steps": len(timed), "warmup": drop + 1})
+                how = (f"stopped at the {budget:.0f} s budget after {len(marks)} of {epochs} rounds; per-round time = "
+                       "period between consecutive per-epoch CSVs written by the reference")
+        if not times or not timed:
             tail = ""
             try:
                 tail = open(os.path.join(base, "server.log")).read()[-400:].replace("\n", " | ")
             except Exception:
                 pass
-            out["unavailable"] = f"reference run failed rc={rc}: {tail}"
+            out["unavailable"] = f"reference run failed rc={rc} truncated={truncated}: {tail}"
         else:
-            times = [float(x) for x in open(ts_path).read().split()]
-            timed = times[-args.steps:]
             sec = sum(timed)
+            k = len(timed)
             out.update({
-                "value": args.steps / sec, "ms_per_step": 1e3 * sec / args.steps, "vs_baseline": (args.steps / sec) / PUBLISHED_EPOCHS_PER_S,
-                "e2e": {"value": args.steps / sec, "unit": "federated_epochs/s",
+                "value": k / sec, "ms_per_step": 1e3 * sec / k, "vs_baseline": (k / sec) / PUBLISHED_EPOCHS_PER_S,
+                "e2e": {"value": k / sec, "unit": "federated_epochs/s",
                         "note": "the reference's round is end to end by construction (numpy sampling + H2D every step, D2H + CPU sampling + CSV every round)"},
-                "timing": "reference's own per-round wall clock (timestamp_experiment.csv), warm-up rounds dropped",
-                "total_wall_s": round(wall, 1), "per_round_s": [round(t, 3) for t in times],
-                "config": {"table": f"{schema.name}-shape synthetic {schema.rows}x{len(schema.columns)}", "clients": n_clients,
-                           "split": "iid", "batch_per_client": 500, "sample_rows_per_round": 40000,
-                           "code": "baseline/_ref/dtds (unmodified Server/dtds), torch RPC TensorPipe, CPU aggregation"},
+                "timing": how, "total_wall_s": round(wall, 1), "per_round_s": [round(t, 3) for t in times],
+                "config": {"model": "CTGAN G(128+n_opt,(256,256)) / PacGAN-10 D((256,256))",
+                           "table": f"{schema.name}-shape synthetic {n_rows}x{len(schema.columns)}", "clients": n_clients,
+                           "split": mode, "global_batch": 500 * n_clients, "batch_per_client": 500, "seq_len": None,
+                           "local_steps_per_round": max(shard_rows) // 500, "rows_per_client": shard_rows[0],
+                           "sample_rows_per_round": 40000, "parallelism": f"federated-dp{n_clients}",
+                           "aggregation": "torch RPC (TensorPipe) gather + CPU average_model + RPC broadcast",
+                           "code": "baseline/_ref/dtds (unmodified Server/dtds), own run() entry point"},
             })
         print(json.dumps(out), flush=True)
     if world > 1:

@@ -45,7 +45,10 @@ def parse():
     p.add_argument("--impl", choices=["ours", "reference"], default="ours")
     p.add_argument("--config", default="adult", choices=["adult", "intrusion", "covertype", "credit", "wide"])
     p.add_argument("--rows", type=int, default=None)
-    p.add_argument("--precision", default="tf32", choices=["tf32", "fp32"])
+    p.add_argument("--precision", default="fp32x3", choices=["fp32x3", "tf32", "fp32"],
+                   help="fp32x3 = 3xTF32 split on tcgen05 (fp32-equivalent, matches the fp32 reference; headline), "
+                        "tf32 = single-pass tcgen05, fp32 = CUDA cores")
+    p.add_argument("--no-alt", action="store_true", help="skip the second (tf32) measurement")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-l2-flush", action="store_true")
     p.add_argument("--out_dir", default=None)
@@ -224,17 +227,36 @@ def run_ours(args):
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
     if hasattr(client, "symm") and client.symm is not None:
         client.symm.check()
+    agg_check = None
+    if world > 1 and getattr(client, "symm", None) is not None:
+        agg_check = check_aggregation(client, group, server, weights, world, rank, dev)
+    # second measurement, single-pass tf32 (the headline above is fp32-equivalent like the reference)
+    alt = None
+    if not args.no_alt and args.precision != "tf32":
+        native.set_precision("tf32")
+        client._graph = None                     # re-capture the iteration with the tf32 kernels
+        server._gen_graph = None
+        for i in range(3):
+            one_round(f"wa{i}", False)
+        server.drain()
+        ms_a, _ = timed(args.steps, False, "a")
+        alt = {"dtype": "tf32", "value": args.steps / (ms_a / 1e3), "ms_per_step": ms_a / args.steps,
+               "note": "same run with single-pass tcgen05 kind::tf32 GEMMs (lower precision than the fp32 reference)"}
+        native.set_precision(args.precision)
     value = args.steps / (ms / 1e3)
     steps_per_epoch = client.steps_per_epoch
     result = {
         "metric": "federated_epochs_per_sec", "value": value, "unit": "federated_epochs/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": value / PUBLISHED_EPOCHS_PER_S, "dtype": "tf32" if args.precision == "tf32" else "fp32",
+        "scaling": "strong", "vs_baseline": value / PUBLISHED_EPOCHS_PER_S, "dtype": {"fp32x3": "fp32 (3xTF32)", "tf32": "tf32", "fp32": "fp32"}[args.precision],
         "data": "synthetic", "impl": "ours", "gpu_launches": launches, "e2e": e2e, "clocks": clocks,
+        "simt_fallbacks": native.simt_fallback_count(), "agg_check": agg_check, "alt_precision": alt,
         "config": {
             "model": "CTGAN G(128+n_opt,(256,256)) / PacGAN-10 D((256,256))" if args.config != "wide" else "CTGAN 1024-wide",
             "table": f"{schema.name}-shape synthetic {len(df)}x{len(schema.columns)}",
             "clients": n_clients, "split": mode, "global_batch": cfg.batch_size * n_clients, "batch_per_client": cfg.batch_size,
+            "gemm": {"fp32x3": "tcgen05 kind::tf32 x3 (hi/lo split, fp32-equivalent products, fp32 accumulate in TMEM)",
+                     "tf32": "tcgen05 kind::tf32 single pass", "fp32": "CUDA-core FMA"}[args.precision],
             "seq_len": None, "local_steps_per_round": steps_per_epoch, "rows_per_client": len(shard),
             "sample_rows_per_round": cfg.sample_rows, "parallelism": f"federated-dp{n_clients}",
             "aggregation": ("fused NVLS multimem kernel" if os.environ.get("FEDTGAN_AGGREGATION") == "nvls"
@@ -251,6 +273,50 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def check_aggregation(client, group, server, weights, world, rank, dev):
+    """Driver-visible correctness of the cross-GPU path (outside the timed region): (i) after training,
+    every rank's replica is bit-identical; (ii) one more fused aggregation of deliberately DIFFERENT
+    replicas equals torch's sum_i w_i theta_i on gathered copies; (iii) replicas identical again."""
+    import torch
+    import torch.distributed as dist
+
+    e = client.engine
+    n = e.G.numel + e.D.numel
+    flat = client.symm.tensor[:n]
+    torch.cuda.synchronize()
+    parts = [torch.empty(n, dtype=torch.float32, device=dev) for _ in range(world)]
+    dist.all_gather(parts, flat.clone())
+    same_before = all(torch.equal(parts[0], q) for q in parts[1:])
+    saved = flat.clone()
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)
+    flat.add_(torch.randn(n, generator=g, device=dev) * 1e-2)
+    dist.all_gather(parts, flat.clone())
+    torch.cuda.synchronize()
+    dist.barrier()
+    group.aggregate(weights, server._round_id())
+    client.symm.check()
+    torch.cuda.synchronize()
+    expect = parts[0] * float(weights[0])
+    for q, w in zip(parts[1:], weights[1:]):
+        expect += q * float(w)
+    keep = torch.ones(n, dtype=torch.bool, device=dev)
+    ints = list(e.G.int_slot_offsets())
+    if ints:
+        keep[torch.tensor(ints, device=dev, dtype=torch.long)] = False      # truncated integer slots
+    err = float((flat - expect)[keep].abs().max())
+    scale = float(expect[keep].abs().max())
+    after = [torch.empty(n, dtype=torch.float32, device=dev) for _ in range(world)]
+    dist.all_gather(after, flat.clone())
+    same_after = all(torch.equal(after[0], q) for q in after[1:])
+    flat.copy_(saved)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ok = same_before and same_after and err <= 1e-6 * max(scale, 1.0) + 1e-7
+    return {"ok": bool(ok), "replicas_bit_identical_after_training": bool(same_before),
+            "max_abs_err_vs_torch_weighted_sum": err, "max_abs_value": scale,
+            "replicas_bit_identical_after_check": bool(same_after), "elements": int(n)}
 
 
 # ------------------------------------------------------------------- reference

@@ -10,6 +10,12 @@
 //   so forward (X.W^T), dgrad (dY.W) and wgrad (dY^T.X) need no transposed copies;
 // * warp roles: warp 0 lane 0 = TMA producer, warp 1 = TMEM allocator + lane 0 MMA issuer,
 //   warps 2..5 = epilogue (each owns one 32-lane TMEM quadrant); 6-stage mbarrier ring;
+// * fp32x3 mode (template X3, ftg_gemm_args::x3): fp32-equivalent products on the tensor cores.  After a
+//   stage has landed, the four epilogue warps split it in shared memory into hi = rna_tf32(x) (in
+//   place) and lo = rna_tf32(x - hi) (second buffer of the stage) and the issuer accumulates
+//   A_lo.B_hi + A_hi.B_lo + A_hi.B_hi into the same TMEM tile (3xTF32; the dropped lo.lo term is
+//   ~2^-22 relative).  Matches the reference's fp32 matmuls (torch allow_tf32=False) to fp32
+//   round-off while staying on tcgen05.
 // * split-K: grid.z CTAs write partial tiles to a caller-provided workspace; the CTA that
 //   arrives last at the tile's counter reduces them in fixed z order (deterministic) and
 //   applies the fused epilogue.  The CTGAN shapes are skinny (M = 50..500, K up to ~8000),
@@ -29,8 +35,22 @@ constexpr int B_STAGE_BYTES = BN * BK * 4;      //  8 KB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int TMEM_COLS = 64;
 constexpr int NUM_THREADS = 192;
-constexpr int smem_bytes(int stages) { return stages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/; }
+constexpr int MAX_STAGES_X3 = 4;                // fp32x3: a stage carries hi and lo copies (48 KB)
+constexpr int smem_bytes(int stages, bool x3 = false) {
+  return stages * STAGE_BYTES * (x3 ? 2 : 1) + 1024 /*align slack*/ + 256 /*barriers*/;
+}
 constexpr int SMEM_BYTES = smem_bytes(MAX_STAGES);
+static_assert(smem_bytes(MAX_STAGES_X3, true) <= 227 * 1024, "fp32x3 ring does not fit shared memory");
+
+// hi/lo split of one fp32 for 3xTF32: hi = round-to-nearest tf32, lo = round-to-nearest tf32 of the
+// (exactly representable) remainder.
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+  uint32_t h, l;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
+  hi = __uint_as_float(h);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(x - hi));
+  lo = __uint_as_float(l);
+}
 constexpr uint32_t SPIN_LIMIT = 1u << 24;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -53,6 +73,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
     if (!done && ++spins > SPIN_LIMIT) __trap();   // never hang the GPU on a protocol bug
   }
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
   asm volatile(
@@ -187,22 +210,24 @@ __device__ int g_gemm_timeline_on = 0;
 
 // 112 registers: two (or three) CTAs fit one SM when the ring is shallow, so that on multi-wave
 // grids one CTA's prologue / epilogue latency hides under its neighbours' main loops.
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, bool X3>
 __global__ void __maxnreg__(112)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
           const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters,
           int vec_ok_i, int cluster_mode, int STAGES) {
   const bool vec_ok = vec_ok_i != 0;
+  constexpr int STG = X3 ? 2 * STAGE_BYTES : STAGE_BYTES;   // fp32x3: [A_hi | B_hi | A_lo | B_lo] per stage
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;            // SWIZZLE_128B tiles need 1024 B alignment
   unsigned char* gen_base = smem_raw + (base - raw);
-  const uint32_t bars = base + STAGES * STAGE_BYTES;      // full[S], empty[S], tmem_full, tmem_slot, flag
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + STAGES * STAGE_BYTES + 8 * (2 * STAGES + 1));
-  volatile int* last_flag = reinterpret_cast<volatile int*>(gen_base + STAGES * STAGE_BYTES + 8 * (2 * STAGES + 1) + 8);
+  const uint32_t bars = base + STAGES * STG;               // full[S], empty[S], tmem_full, tmem_slot, flag, split[S]
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gen_base + STAGES * STG + 8 * (2 * STAGES + 1));
+  volatile int* last_flag = reinterpret_cast<volatile int*>(gen_base + STAGES * STG + 8 * (2 * STAGES + 1) + 8);
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
   const uint32_t tmem_full_bar = bars + 8u * (2 * STAGES);
+  auto split_bar = [&](int s) { return bars + 8u * (2 * STAGES + 3 + s); };   // hi/lo copies of stage s are ready
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM, z = blockIdx.z;
@@ -215,6 +240,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   if (threadIdx.x == 0) {
     TL(0);
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    if (X3) for (int s = 0; s < STAGES; ++s) mbar_init(split_bar(s), 4);      // one arrival per splitter warp
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -239,7 +265,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     TL(1);
     for (int kb = kb0; kb < kb1; ++kb) {
       mbar_wait(empty_bar(s), phase ^ 1u);
-      const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
+      const uint32_t sa = base + s * STG, sb = sa + A_STAGE_BYTES;
       mbar_expect_tx(full_bar(s), STAGE_BYTES);
       const int k = kb * BK;
       if (A_MN) {
@@ -265,10 +291,10 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     int s = 0;
     uint32_t phase = 0;
     for (int kb = kb0; kb < kb1; ++kb) {
-      mbar_wait(full_bar(s), phase);
+      mbar_wait(X3 ? split_bar(s) : full_bar(s), phase);
       if (kb == kb0) TL(3);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t sa = base + s * STAGE_BYTES, sb = sa + A_STAGE_BYTES;
+      const uint32_t sa = base + s * STG, sb = sa + A_STAGE_BYTES;
 #pragma unroll
       for (int ks = 0; ks < BK / 8; ++ks) {
         // K-major : 8 tf32 = 32 B step inside the 128 B swizzle row; SBO = 8 rows * 128 B
@@ -276,7 +302,18 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         //           32-element MN chunk is the next TMA box (LBO = BK * 128 B); 8 k-rows = 1024 B step
         uint64_t ad = A_MN ? make_desc(sa + ks * 1024, BK * 128, 512, 1) : make_desc(sa + ks * 32, 16, 1024, 2);
         uint64_t bd = B_MN ? make_desc(sb + ks * 1024, BK * 128, 512, 1) : make_desc(sb + ks * 32, 16, 1024, 2);
-        umma_tf32(tmem_base, ad, bd, idesc, (kb > kb0 || ks > 0) ? 1u : 0u);
+        const uint32_t acc0 = (kb > kb0 || ks > 0) ? 1u : 0u;
+        if (X3) {
+          // lo copies sit STAGE_BYTES above their hi twins; small cross terms first
+          const uint32_t la = sa + STAGE_BYTES, lb = sb + STAGE_BYTES;
+          uint64_t adl = A_MN ? make_desc(la + ks * 1024, BK * 128, 512, 1) : make_desc(la + ks * 32, 16, 1024, 2);
+          uint64_t bdl = B_MN ? make_desc(lb + ks * 1024, BK * 128, 512, 1) : make_desc(lb + ks * 32, 16, 1024, 2);
+          umma_tf32(tmem_base, adl, bd, idesc, acc0);
+          umma_tf32(tmem_base, ad, bdl, idesc, 1u);
+          umma_tf32(tmem_base, ad, bd, idesc, 1u);
+        } else {
+          umma_tf32(tmem_base, ad, bd, idesc, acc0);
+        }
       }
       umma_commit(empty_bar(s));                // frees the smem slot when these MMAs retire
       if (++s == STAGES) { s = 0; phase ^= 1u; }
@@ -288,6 +325,33 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     const int q = warp & 3;                      // TMEM lane quadrant owned by this warp
     const int row_in_tile = q * 32 + lane;
     const int m = m0 + row_in_tile;
+    if (X3) {
+      // ---- fp32x3 splitter: as each stage lands, rewrite it as hi (in place) + lo (upper half of the stage)
+      const int st = threadIdx.x - 64;
+      int s = 0;
+      uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full_bar(s), phase);
+        float4* hi4 = reinterpret_cast<float4*>(gen_base + s * STG);
+        float4* lo4 = reinterpret_cast<float4*>(gen_base + s * STG + STAGE_BYTES);
+        constexpr int PER = STAGE_BYTES / 16 / 128;        // 12 float4 per thread
+        float4 v[PER];
+#pragma unroll
+        for (int i = 0; i < PER; ++i) v[i] = hi4[i * 128 + st];
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+          float4 h, l;
+          split_tf32(v[i].x, h.x, l.x); split_tf32(v[i].y, h.y, l.y);
+          split_tf32(v[i].z, h.z, l.z); split_tf32(v[i].w, h.w, l.w);
+          hi4[i * 128 + st] = h;
+          lo4[i * 128 + st] = l;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+        __syncwarp();
+        if (lane == 0) mbar_arrive(split_bar(s));
+        if (++s == STAGES) { s = 0; phase ^= 1u; }
+      }
+    }
     mbar_wait(tmem_full_bar, 0);
     if (threadIdx.x == 64) TL(5);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -429,10 +493,6 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
 constexpr int PERSIST_STAGES = 5;
 constexpr int PERSIST_STAGE_TILE_BYTES = BM * SLD * 4;                       // 34 816 B
 constexpr int PERSIST_SMEM_BYTES = PERSIST_STAGES * STAGE_BYTES + PERSIST_STAGE_TILE_BYTES + 1024 + 256;
-
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
 
 template <bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -633,7 +693,7 @@ bool make_map(CUtensorMap* map, const float* ptr, int inner, int outer, int ld, 
 //    share an SM and the grid is resident at once (67 us).
 // FTG_GEMM_STAGES=<n> / ftg_gemm_tc_set_stages force a depth (experiments).
 int g_forced_stages = -1;
-int choose_stages(long long ctas, int kblocks_per_cta, int cluster_size) {
+int choose_stages(long long ctas, int kblocks_per_cta, int cluster_size, bool x3 = false) {
   if (g_forced_stages < 0) {
     const char* e = getenv("FTG_GEMM_STAGES");
     g_forced_stages = e ? atoi(e) : 0;
@@ -643,6 +703,11 @@ int choose_stages(long long ctas, int kblocks_per_cta, int cluster_size) {
   if (forced >= 2 && forced <= MAX_STAGES) s = forced;
   else if (ctas > 148) s = 4;
   else if (cluster_size >= 8 && ctas > 96) s = 4;
+  if (x3) {
+    // a stage is 48 KB (hi + lo): 4 stages fill the SM; multi-wave grids / big clusters keep two CTAs per SM
+    if (s > MAX_STAGES_X3) s = MAX_STAGES_X3;
+    if (!(forced >= 2 && forced <= MAX_STAGES) && (ctas > 148 || (cluster_size >= 8 && ctas > 96))) s = 2;
+  }
   if (s > kblocks_per_cta) s = kblocks_per_cta;
   return s < 2 ? 2 : s;
 }
@@ -657,9 +722,10 @@ bool use_persistent() {
   return g_persistent == 1;
 }
 
-template <bool A_MN, bool B_MN, int EPI>
+template <bool A_MN, bool B_MN, int EPI, bool X3 = false>
 int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
                int vec_ok, cudaStream_t stream) {
+  if (!X3 && p.x3) return launch_epi<A_MN, B_MN, EPI, true>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
   const int cluster_mode = (ws == nullptr && split_k > 1) ? 1 : 0;   // no workspace given: reduce through DSMEM
   // function attributes are per device: one flag per (instantiation, device)
   static std::atomic<bool> attr_done_dev[64];
@@ -667,15 +733,16 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
   if (cudaGetDevice(&dev_id) != cudaSuccess || dev_id < 0 || dev_id >= 64) return FTG_ERR_UNSUPPORTED;
   std::atomic<bool>& attr_done = attr_done_dev[dev_id];
   if (!attr_done.load(std::memory_order_acquire)) {
-    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         X3 ? smem_bytes(MAX_STAGES_X3, true) : SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI, X3>, cudaFuncAttributePreferredSharedMemoryCarveout,
                              cudaSharedmemCarveoutMaxShared);
     if (e != cudaSuccess) return (int)e;
     attr_done.store(true, std::memory_order_release);
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
-  if (use_persistent() && split_k == 1 && (long long)grid.x * grid.y > 148) {
+  if (!X3 && use_persistent() && split_k == 1 && (long long)grid.x * grid.y > 148) {
     static std::atomic<bool> pattr_done_dev[64];
     if (!pattr_done_dev[dev_id].load(std::memory_order_acquire)) {
       cudaError_t e = cudaFuncSetAttribute(k_gemm_tc_persist<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -697,12 +764,12 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
     return (int)cudaLaunchKernelEx(&pc, k_gemm_tc_persist<A_MN, B_MN, EPI>, ma, mb, p, vec_ok, (int)grid.y, (int)grid.x);
   }
   const int stages = choose_stages((long long)grid.x * grid.y * grid.z, (ftg_cdiv(p.K, BK) + split_k - 1) / split_k,
-                                   cluster_mode ? split_k : 1);
+                                   cluster_mode ? split_k : 1, X3);
   ++g_ftg_launch_count;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = smem_bytes(stages);
+  cfg.dynamicSmemBytes = smem_bytes(stages, X3);
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
@@ -720,8 +787,8 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI>, ma, mb, p, split_k, ws, ctr, vec_ok, cluster_mode,
-                                 stages);
+  return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI, X3>, ma, mb, p, split_k, ws, ctr, vec_ok,
+                                 cluster_mode, stages);
 }
 
 template <bool A_MN, bool B_MN>

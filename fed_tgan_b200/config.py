@@ -38,9 +38,10 @@ class CTGANConfig:
     dp_prior: float = 0.001
     # generation
     sample_rows: int = 40000
-    # GEMM precision on the device path: "tf32" (tcgen05 kind::tf32, fp32 accumulate in
-    # TMEM) or "fp32" (CUDA-core FMA kernels)
-    precision: str = "tf32"
+    # GEMM arithmetic on the device path (applied by TrainEngine): "fp32x3" (default; tcgen05 with the
+    # 3xTF32 hi/lo split, fp32-equivalent like the reference's fp32 matmuls), "tf32" (single-pass
+    # tcgen05 kind::tf32, opt-in) or "fp32" (CUDA-core FMA kernels)
+    precision: str = "fp32x3"
     seed: int = 0
 
     def __post_init__(self):

@@ -42,6 +42,7 @@ class GemmArgs(C.Structure):
         ("rng_state", _vp), ("rng_stream", _i),
         ("alpha", _f), ("slope", _f), ("drop_p", _f),
         ("accumulate", _i),
+        ("x3", _i),
     ]
 
 
@@ -141,7 +142,12 @@ def _ld(t):
 
 
 # ----------------------------------------------------------------- precision
-_precision = os.environ.get("FEDTGAN_PRECISION", "tf32")
+# "fp32x3": tcgen05 with the 3xTF32 hi/lo split (fp32-equivalent products; the default -- the reference
+#           trains with fp32 matmuls);  "tf32": single-pass tcgen05 kind::tf32 (opt-in, 10-bit mantissa
+#           products);  "fp32": exact fp32 on the CUDA cores (k_gemm_simt, the oracle / fallback).
+PRECISIONS = ("fp32x3", "tf32", "fp32")
+_precision = os.environ.get("FEDTGAN_PRECISION", "fp32x3")
+_simt_fallbacks = 0          # tensor-core launches that fell back to k_gemm_simt (unaligned operands)
 _splitk_mode = os.environ.get("FEDTGAN_SPLITK", "cluster")     # "cluster" (DSMEM) | "workspace"
 _scratch = {}
 MAX_WS_BYTES = 64 << 20
@@ -149,12 +155,18 @@ MAX_WS_BYTES = 64 << 20
 
 def set_precision(p: str):
     global _precision
-    assert p in ("tf32", "fp32")
+    assert p in PRECISIONS, p
     _precision = p
 
 
 def get_precision() -> str:
     return _precision
+
+
+def simt_fallback_count() -> int:
+    """How many GEMMs asked for the tensor cores but ran on the CUDA-core kernel because an operand was
+    not 16 B aligned / its leading dimension not a multiple of 4 floats.  Should stay 0."""
+    return _simt_fallbacks
 
 
 def _scratch_for(device, stream):
@@ -205,7 +217,8 @@ def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None
     g = _gemm_args(a, b, out, a_t, b_t, bias, act, mask_in, mask_out, u, rng, stream, accumulate, alpha, slope, p)
     prec = precision or _precision
     st = _stream()
-    if prec == "tf32":
+    if prec in ("tf32", "fp32x3"):
+        g.x3 = 1 if prec == "fp32x3" else 0
         ws = ctr = None
         if split_k is None and splitk_mode == "cluster":
             sk = _choose_cluster_split(g.M, g.N, g.K)        # DSMEM reduction inside a cluster: no scratch
@@ -223,6 +236,14 @@ def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None
             return out
         if rc != UNSUPPORTED:
             raise NativeError(f"ftg_gemm_tc failed with code {rc}")
+        global _simt_fallbacks
+        _simt_fallbacks += 1
+        if _simt_fallbacks == 1:
+            import warnings
+
+            warnings.warn(f"tcgen05 GEMM not applicable to M={g.M} N={g.N} K={g.K} lda={g.lda} ldb={g.ldb} "
+                          "(pointers must be 16 B aligned, leading dimensions multiples of 4 floats): running the "
+                          "CUDA-core fp32 kernel instead; see native.simt_fallback_count()")
     _ck(_gemm_simt(C.byref(g), st), "ftg_gemm_simt")
     return out
 

@@ -68,7 +68,7 @@ def _on_device(fn):
 class MDGANClient:
     def __init__(self, datapath, selected_variables, categorical_list, nonnegative_list, date_dic, target_column,
                  problem_type, epochs, device=None, config: CTGANConfig | dict | None = None, dataframe=None,
-                 vgm_backend="sklearn", write_side_files=True, client_id=0, **kwargs):
+                 vgm_backend="sklearn", write_side_files=True, client_id=0, split=None, **kwargs):
         if isinstance(config, dict):
             config = CTGANConfig.from_dict(config)
         self.cfg = config if config is not None else CTGANConfig(**kwargs)
@@ -87,6 +87,14 @@ class MDGANClient:
         self.problem_type = problem_type
         self.vgm_backend = vgm_backend
         self.write_side_files = write_side_files
+        if split is not None and dataframe is None:
+            # (mode, n_clients, index, seed): every client reads the same file and keeps its own shard
+            import pandas as pd
+
+            from ..data.schemas import split_table
+
+            mode, n_shards, idx, sseed = split
+            dataframe = split_table(pd.read_csv(datapath), int(n_shards), mode, seed=int(sseed))[int(idx)]
         self._dataframe = dataframe
         self.meta_file = prepare_data(self.datapath, self.selected_variables, self.categorical_list,
                                       self.nonnegative_list, self.date_dic, self.target_column, self.problem_type,
@@ -259,6 +267,8 @@ class MDGANClient:
     @_on_device
     def checkpoint_state(self):
         e = self.engine
+        if self.symm is not None:
+            self.symm.check()        # never checkpoint an arena a timed-out aggregation left half-averaged
         return {
             "G": e.G.state_dict(), "D": e.D.state_dict(),
             "optG": e.G.optimizer_state(int(e.rng.state[1].item())),

@@ -240,7 +240,7 @@ class SpmdGroup(ClientGroup):
                 self.client.symm_setup_nvls(self.pg)
                 self._symm_ready = True
                 return
-            except RuntimeError as exc:
+            except (RuntimeError, ImportError) as exc:
                 warnings.warn(f"NVLS aggregation unavailable ({exc}); using the P2P two-shot kernel")
         handle = self.client.symm_export()
         handles = [None] * self.n

@@ -74,7 +74,13 @@ def build_parser():
     p.add_argument("--batch_size", type=int, default=500)
     p.add_argument("--gen_dim", type=_csv_list, default=[256, 256])
     p.add_argument("--dis_dim", type=_csv_list, default=[256, 256])
-    p.add_argument("--precision", choices=["tf32", "fp32"], default="tf32")
+    p.add_argument("--precision", choices=["fp32x3", "tf32", "fp32"], default="fp32x3",
+                   help="GEMM arithmetic: fp32x3 = 3xTF32 split on the tensor cores (fp32-equivalent, matches the "
+                        "reference's fp32 matmuls; default), tf32 = single-pass tensor cores (opt-in), fp32 = CUDA cores")
+    p.add_argument("--split", choices=["none", "iid", "skewed"], default="none",
+                   help="all clients read the same -datapath and each keeps its own horizontal shard of it "
+                        "(iid: equal random shards; skewed: unequal, sorted by the first column)")
+    p.add_argument("--split_seed", type=int, default=0)
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--rpc_timeout", type=float, default=600.0)
     p.add_argument("--checkpoint_every", type=int, default=0)
@@ -91,8 +97,20 @@ def config_from_args(args) -> CTGANConfig:
                        precision=args.precision, seed=args.seed)
 
 
-def client_kwargs(args, cfg, client_id, device):
-    return dict(datapath=args.datapath, selected_variables=args.selected_variables,
+def resolve_datapath(template: str, client_id: int) -> str:
+    """``-datapath`` may carry ``{rank}`` (1-based RPC rank of the client, as in the reference's
+    ``Client<k>`` folders) and/or ``{client}`` (0-based client id) so that every client of a one-box
+    launch reads its OWN file; the reference gets the same effect from one working directory per client
+    (``README.md:12``)."""
+    return template.replace("{rank}", str(client_id + 1)).replace("{client}", str(client_id))
+
+
+def client_kwargs(args, cfg, client_id, device, n_clients=None):
+    split = None
+    if getattr(args, "split", "none") != "none" and n_clients and n_clients > 1:
+        split = (args.split, int(n_clients), int(client_id), int(getattr(args, "split_seed", 0)))
+    return dict(datapath=resolve_datapath(args.datapath, client_id), split=split,
+                selected_variables=args.selected_variables,
                 categorical_list=args.categorical_list, nonnegative_list=args.nonnegative_list,
                 date_dic=args.date_dic, target_column=args.target_column, problem_type=args.problem_type,
                 epochs=args.epochs, config=cfg.to_dict(), device=device, vgm_backend=args.vgm_backend,
@@ -115,15 +133,33 @@ def federate(server: MDGANServer, verbose=True):
     return server.fit()
 
 
+def _warn_shared_datapath(args, n_clients):
+    if n_clients > 1 and getattr(args, "split", "none") == "none" and "{" not in args.datapath:
+        import warnings
+
+        warnings.warn(f"all {n_clients} clients resolve -datapath to the same file '{args.datapath}': unless every "
+                      "client process runs in its own working directory they train on identical data and the "
+                      "similarity weights degenerate to 1/N.  Use '{rank}'/'{client}' in -datapath or --split iid|skewed.")
+
+
 def _client_device(rank, force_cpu):
     if force_cpu or not torch.cuda.is_available():
         return "cpu"
     return f"cuda:{(rank - 1) % torch.cuda.device_count()}"
 
 
+def _apply_precision(cfg):
+    """The CLI's --precision reaches the kernels through the process-wide switch of ops.native."""
+    if torch.cuda.is_available():
+        from ..ops import native
+
+        native.set_precision(cfg["precision"] if isinstance(cfg, dict) else cfg.precision)
+
+
 def _make_remote_client(kwargs):
     if str(kwargs.get("device", "cpu")).startswith("cuda"):
         torch.cuda.set_device(torch.device(kwargs["device"]))
+        _apply_precision(kwargs["config"])
     return MDGANClient(**kwargs)
 
 
@@ -143,16 +179,22 @@ def run(rank, einterval, world_size, ip, port, name, datapath, selected_variable
                                            init_method=f"tcp://{ip}:{port}")
     cfg = config_from_args(args)
     if rank == 0:
+        if torch.cuda.is_available() and not args.cpu:
+            _apply_precision(cfg)
         print("number of training epochs: ", epochs)
         print("world size: ", world_size, f"tcp://{ip}:{port}")
         rpc.init_rpc("server", rank=0, world_size=world_size, rpc_backend_options=opts)
         rrefs = []
         for worker in range(1, world_size):
-            kw = client_kwargs(args, cfg, worker - 1, _client_device(worker, args.cpu))
+            kw = client_kwargs(args, cfg, worker - 1, _client_device(worker, args.cpu), world_size - 1)
             rrefs.append(rpc.remote(f"client{worker}", _make_remote_client, args=(kw,)))
             print(f"register remote client{worker}")
         on_gpu = torch.cuda.is_available() and not args.cpu
-        group = RpcGroup(rrefs, use_symmetric=on_gpu and world_size > 2,
+        _warn_shared_datapath(args, world_size - 1)
+        # the in-kernel barrier spins: it needs every client on its own GPU (two spinning kernels
+        # time-slicing one GPU can only time out), otherwise fall back to the state-dict exchange
+        one_gpu_each = on_gpu and (world_size - 1) <= torch.cuda.device_count()
+        group = RpcGroup(rrefs, use_symmetric=one_gpu_each and world_size > 2,
                          server_device="cuda:0" if on_gpu else "cpu")
         server = MDGANServer(group, epochs=epochs, config=cfg, name=dataset_name(datapath), out_dir=args.out_dir,
                              vgm_backend=args.vgm_backend, checkpoint_every=args.checkpoint_every,
@@ -175,10 +217,14 @@ def run_spmd(args):
     if not dist.is_initialized():
         dist.init_process_group("nccl" if on_gpu else "gloo", rank=rank, world_size=world)
     cfg = config_from_args(args)
+    if on_gpu:
+        _apply_precision(cfg)
     device = f"cuda:{local}" if on_gpu else "cpu"
     if getattr(args, "aggregation", None):
         os.environ["FEDTGAN_AGGREGATION"] = args.aggregation
-    client = MDGANClient(**client_kwargs(args, cfg, rank, device))
+    if rank == 0:
+        _warn_shared_datapath(args, world)
+    client = MDGANClient(**client_kwargs(args, cfg, rank, device, world))
     server = MDGANServer(SpmdGroup(client), epochs=args.epochs, config=cfg, name=dataset_name(args.datapath),
                          out_dir=args.out_dir, vgm_backend=args.vgm_backend, device=device,
                          checkpoint_every=args.checkpoint_every, resume=args.resume)

@@ -39,12 +39,16 @@ typedef struct {
   const int64_t* rng_state; int rng_stream;
   float alpha, slope, drop_p;
   int accumulate;
+  int x3;   /* ftg_gemm_tc only: 1 = fp32x3 (3xTF32 hi/lo split, fp32-equivalent products), 0 = single-pass tf32 */
 } ftg_gemm_args;
 
 /* fp32 CUDA-core GEMM (exact fp32; fallback + oracle for the tensor-core path) */
 int ftg_gemm_simt(const ftg_gemm_args* args, ftg_stream_t stream);
 
 /* tcgen05 / TMEM / TMA GEMM, kind::tf32 with fp32 accumulation in tensor memory.
+ * args->x3 = 1 selects the fp32-equivalent mode: every operand stage is split in shared memory into
+ * hi = rna_tf32(x) and lo = rna_tf32(x - hi) and A_lo.B_hi + A_hi.B_lo + A_hi.B_hi is accumulated into
+ * the same TMEM tile (3xTF32), which reproduces the reference's fp32 matmuls to fp32 round-off.
  * Split-K partial tiles go through `workspace` (>= ftg_gemm_tc_workspace_bytes(...)) and
  * `tile_counters` (int32, zero-initialised once, >= ftg_gemm_tc_num_tiles(...)); both are
  * caller-owned scratch and may be NULL when the call does not split K.
