@@ -51,6 +51,8 @@ def parse():
     p.add_argument("--no-alt", action="store_true", help="skip the second (tf32) measurement")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-l2-flush", action="store_true")
+    p.add_argument("--diag-no-generation", action="store_true",
+                   help="DIAGNOSTIC ONLY (not a valid headline): skip the 40 000-row generation + CSV of every round")
     p.add_argument("--out_dir", default=None)
     p.add_argument("--rotate", action="store_true", help="rotate the generate/write-CSV duty over the ranks")
     return p.parse_args()
@@ -179,7 +181,8 @@ def run_ours(args):
             client.restage_shard()
         client.run_local_epochs(1)
         group.aggregate(weights, server._round_id())
-        server.sample_data(i, wait=False)
+        if not args.diag_no_generation:
+            server.sample_data(i, wait=False)
         if e2e:
             client.read_losses()
 
@@ -249,7 +252,7 @@ def run_ours(args):
         "metric": "federated_epochs_per_sec", "value": value, "unit": "federated_epochs/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": value / PUBLISHED_EPOCHS_PER_S, "dtype": {"fp32x3": "fp32 (3xTF32)", "tf32": "tf32", "fp32": "fp32"}[args.precision],
-        "data": "synthetic", "impl": "ours", "gpu_launches": launches, "e2e": e2e, "clocks": clocks,
+        "data": "synthetic", "impl": "ours", **({"INVALID_diagnostic": "generation skipped"} if args.diag_no_generation else {}), "gpu_launches": launches, "e2e": e2e, "clocks": clocks,
         "simt_fallbacks": native.simt_fallback_count(), "agg_check": agg_check, "alt_precision": alt,
         "config": {
             "model": "CTGAN G(128+n_opt,(256,256)) / PacGAN-10 D((256,256))" if args.config != "wide" else "CTGAN 1024-wide",

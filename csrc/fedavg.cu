@@ -66,7 +66,9 @@ struct Peers {
   float* p[MAX_WORLD];
   int* f[MAX_WORLD];
   float w[MAX_WORLD];
+  const float* wdev;        // non-null: the weights live in device memory (output of ftg_fed_stats_to_weights)
 };
+__device__ __forceinline__ float peer_weight(const Peers& P, int i) { return P.wdev ? __ldg(P.wdev + i) : P.w[i]; }
 
 // ------------------------------------------------------------------- local
 __global__ void k_fedavg_local(Peers P, int world, long long n4, IntSlots slots) {
@@ -75,7 +77,7 @@ __global__ void k_fedavg_local(Peers P, int world, long long n4, IntSlots slots)
 #pragma unroll 4
     for (int i = 0; i < world; ++i) {
       float4 v = reinterpret_cast<const float4*>(P.p[i])[q];
-      float w = P.w[i];
+      float w = peer_weight(P, i);
       acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y); acc.z = fmaf(w, v.z, acc.z); acc.w = fmaf(w, v.w, acc.w);
     }
     if (slots.n) acc = trunc_slots(acc, q * 4, slots);
@@ -135,7 +137,7 @@ k_fedavg_twoshot(Peers P, int rank, int world, long long n4, IntSlots slots, int
 #pragma unroll
       for (int i = 0; i < W; ++i)
         if (i < world) {
-          const float w = P.w[i];
+          const float w = peer_weight(P, i);
           acc.x = fmaf(w, v[u][i].x, acc.x); acc.y = fmaf(w, v[u][i].y, acc.y);
           acc.z = fmaf(w, v[u][i].z, acc.z); acc.w = fmaf(w, v[u][i].w, acc.w);
         }
@@ -182,7 +184,7 @@ k_fedavg_oneshot(Peers P, float* staging, int rank, int world, long long n4, Int
 #pragma unroll 4
     for (int i = 0; i < world; ++i) {
       float4 v = reinterpret_cast<const float4*>(P.p[i])[q];
-      float w = P.w[i];
+      float w = peer_weight(P, i);
       acc.x = fmaf(w, v.x, acc.x); acc.y = fmaf(w, v.y, acc.y); acc.z = fmaf(w, v.z, acc.z); acc.w = fmaf(w, v.w, acc.w);
     }
     if (slots.n) acc = trunc_slots(acc, q * 4, slots);
@@ -240,7 +242,7 @@ k_fedavg_nvls(Peers P, float* mc_base, int rank, int world, long long n4, IntSlo
   // phase 0: theta_rank *= w_rank (whole local replica), then tell the peers
   {
     float4* mine = reinterpret_cast<float4*>(P.p[rank]);
-    const float w = P.w[rank];
+    const float w = peer_weight(P, rank);
     const long long stride0 = (long long)gridDim.x * blockDim.x;
     for (long long q0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < n4; q0 += stride0 * 4) {
       float4 v[4];
@@ -314,10 +316,16 @@ int fill(Peers& P, IntSlots& S, float* const* arenas, int* const* flags, int wor
          const int* int_offsets, int n_int) {
   if (world < 1 || world > MAX_WORLD || n_int > MAX_INT) return FTG_ERR_UNSUPPORTED;
   for (int i = 0; i < MAX_WORLD; ++i) { P.p[i] = nullptr; P.f[i] = nullptr; P.w[i] = 0.f; }
+  // `weights` may be a device pointer: then the kernel reads it at run time
+  cudaPointerAttributes at;
+  const bool on_device = cudaPointerGetAttributes(&at, weights) == cudaSuccess &&
+                         (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
+  cudaGetLastError();       // a plain host pointer makes older runtimes report an (ignorable) error
+  P.wdev = on_device ? weights : nullptr;
   for (int i = 0; i < world; ++i) {
     P.p[i] = arenas[i];
     P.f[i] = flags ? flags[i] : nullptr;
-    P.w[i] = weights[i];
+    if (!on_device) P.w[i] = weights[i];
   }
   S.n = n_int;
   for (int k = 0; k < n_int; ++k) S.off[k] = int_offsets[k];

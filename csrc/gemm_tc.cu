@@ -36,11 +36,14 @@ constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int TMEM_COLS = 64;
 constexpr int NUM_THREADS = 192;
 constexpr int MAX_STAGES_X3 = 4;                // fp32x3: a stage carries hi and lo copies (48 KB)
-constexpr int smem_bytes(int stages, bool x3 = false) {
-  return stages * STAGE_BYTES * (x3 ? 2 : 1) + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int smem_bytes(int stages, bool x3 = false, bool push = false) {
+  return stages * STAGE_BYTES * (x3 ? 2 : 1) + 1024 /*align slack*/ + 256 /*barriers*/ +
+         (push ? BM * BN * 4 + 8 * 3 * BN * 4 : 0) /*receive buffers of the push-based cluster reduction*/;
 }
 constexpr int SMEM_BYTES = smem_bytes(MAX_STAGES);
 static_assert(smem_bytes(MAX_STAGES_X3, true) <= 227 * 1024, "fp32x3 ring does not fit shared memory");
+static_assert(smem_bytes(MAX_STAGES_X3 - 1, true, true) <= 227 * 1024, "fp32x3 cluster ring does not fit shared memory");
+static_assert(smem_bytes(MAX_STAGES, false, true) <= 227 * 1024, "tf32 cluster ring does not fit shared memory");
 
 // hi/lo split of one fp32 for 3xTF32: hi = round-to-nearest tf32, lo = round-to-nearest tf32 of the
 // (exactly representable) remainder.
@@ -107,6 +110,30 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
       : "memory");
 }
 
+// Asynchronous 16 B store into ANOTHER CTA's shared memory (same cluster) that signals `bytes` on an
+// mbarrier of that CTA when it lands: the receiving side waits on its own barrier, nobody synchronises
+// the whole cluster.  Addresses are shared::cluster addresses (mapa).
+__device__ __forceinline__ void st_async_v4(uint32_t remote_addr, float4 v, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
+               ::"r"(remote_addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w), "r"(remote_bar) : "memory");
+}
+__device__ __forceinline__ uint32_t map_cluster(uint32_t local_addr, int cta_rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(cta_rank));
+  return remote;
+}
+constexpr int RECV_BYTES = BM * BN * 4;               // push split-K: one slot per source rank, R rows x 64 floats each
+constexpr int STAT_RECV_BYTES = 8 * 3 * BN * 4;       // BatchNorm statistics of up to 8 cluster CTAs
+constexpr int CLUSTER_EXTRA_BYTES = RECV_BYTES + STAT_RECV_BYTES;
+
+// lo part relative to the hardware's own truncation of x to tf32 (x3 mode 2)
+__device__ __forceinline__ float lo_trunc_tf32(float x) {
+  const float hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+  uint32_t l;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(x - hi));
+  return __uint_as_float(l);
+}
+
 // Shared-memory matrix descriptor (sm_100 descriptor version 1).
 //   bits [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout
 //   layout 2 = SWIZZLE_128B (16 B atomicity)   : K-major operands
@@ -127,7 +154,7 @@ constexpr int CHUNKS = (BM * BN / 4) / 128;      // float4 chunks per epilogue t
 constexpr int EPI_BATCH = CHUNKS / 2;
 
 // Epilogue specialisations (compile-time, so the unrolled code stays tiny and branch-free).
-enum { EPI_PLAIN = 0, EPI_ACC = 1, EPI_BIAS = 2, EPI_BIAS_ACT = 3, EPI_MASK = 4, EPI_GENERIC = 5 };
+enum { EPI_PLAIN = 0, EPI_ACC = 1, EPI_BIAS = 2, EPI_BIAS_ACT = 3, EPI_MASK = 4, EPI_GENERIC = 5, EPI_BN = 6 };
 
 // Ragged / unaligned chunk (and the generic flag combination): element-wise path, out of line
 // because it is cold; `p` by value so that the kernel itself never spills its parameters.
@@ -203,6 +230,198 @@ __device__ __forceinline__ void epilogue_tile(const ftg_gemm_args& p, bool vec_o
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// EPI_BN: Linear -> BatchNorm1d(train) -> ReLU -> concat-store as the GEMM's epilogue (SURVEY K2;
+// reference Residual, S/dtds/synthesizers/ctgan.py:33-44).
+//
+// The CTAs of one 64-column panel -- all M-tiles (cluster dim y = gridDim.y <= 4) times the split-K
+// factor (cluster dim z) -- form one thread-block cluster.  After the split-K partials have been
+// summed through distributed shared memory, CTA (y, z) owns rows [z*128/S, (z+1)*128/S) of M-tile y.
+// It computes (count, mean, M2) of its rows per column (two local passes over its shared-memory
+// slice), publishes them in shared memory, and after one cluster barrier every CTA merges the
+// triplets of all cluster CTAs with Chan's parallel-variance formula (fixed order: deterministic,
+// no E[x^2]-mean^2 cancellation).  Then each CTA normalises its own slice and stores BOTH the
+// pre-activation (kept for the backward pass) and relu(bn(.)) into its column window of the wide
+// activation buffer.  CTA (0, 0) of the cluster updates running_mean / running_var (momentum,
+// unbiased variance) and the saved batch statistics.
+constexpr int BN_STAT_OFF = BM * SLD * 4;            // bytes: red[2][4][64] floats, then stat[3][64] floats
+constexpr int BN_RED_FLOATS = 2 * 4 * BN;
+static_assert(BN_STAT_OFF + (BN_RED_FLOATS + 3 * BN) * 4 <= 2 * STAGE_BYTES, "BN scratch must fit the idle operand ring");
+
+__device__ __forceinline__ float4 bn_colreduce(float4 v, float* red, int et) {
+  // threads with equal (et & 15) own the same 4 columns; 8 row groups = 2 per warp x 4 warps
+  v.x += __shfl_xor_sync(0xffffffffu, v.x, 16); v.y += __shfl_xor_sync(0xffffffffu, v.y, 16);
+  v.z += __shfl_xor_sync(0xffffffffu, v.z, 16); v.w += __shfl_xor_sync(0xffffffffu, v.w, 16);
+  const int w = et >> 5, c4 = et & 15;
+  asm volatile("bar.sync 1, 128;" ::: "memory");               // previous use of `red` is over
+  if ((et & 31) < 16) *reinterpret_cast<float4*>(red + w * BN + c4 * 4) = v;
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+  float4 t = *reinterpret_cast<const float4*>(red + c4 * 4);
+#pragma unroll
+  for (int k = 1; k < 4; ++k) {
+    const float4 u = *reinterpret_cast<const float4*>(red + k * BN + c4 * 4);
+    t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+  }
+  return t;
+}
+
+__device__ __forceinline__ void bn_epilogue(const ftg_gemm_args& p, const ftg_bn_args& bn, bool vec_ok,
+                                            unsigned char* gen_base, uint32_t base_u32, int et, int m0, int n0,
+                                            int r, int S, int CY, int y, float* stat_recv, uint32_t stat_recv_u32,
+                                            uint32_t stat_bar) {
+  float* stage = reinterpret_cast<float*>(gen_base);
+  float* red = reinterpret_cast<float*>(gen_base + BN_STAT_OFF);
+  float* stat = red + BN_RED_FLOATS;
+  const int R = BM / S;                                // rows of the tile owned by this CTA
+  const int c4 = et & 15, g = et >> 4;
+  const int n = n0 + c4 * 4;
+  const int row0 = r * R;
+  const int nj = R >> 3;                               // rows per thread (stride 8)
+  int cnt_i = p.M - (m0 + row0);
+  cnt_i = cnt_i < 0 ? 0 : (cnt_i > R ? R : cnt_i);
+  const float cnt = (float)cnt_i;
+  // bias (column-wise shift: does not change the variance, but the stored pre-activation carries it)
+  float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) {
+    bb.x = n + 0 < p.N ? __ldg(p.bias + n + 0) : 0.f; bb.y = n + 1 < p.N ? __ldg(p.bias + n + 1) : 0.f;
+    bb.z = n + 2 < p.N ? __ldg(p.bias + n + 2) : 0.f; bb.w = n + 3 < p.N ? __ldg(p.bias + n + 3) : 0.f;
+  }
+  // ---- pass A: local column sums (and fold alpha / bias into the staged slice)
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int j = 0; j < nj; ++j) {
+    const int row = row0 + g + 8 * j;
+    float4* q = reinterpret_cast<float4*>(stage + row * SLD + c4 * 4);
+    float4 v = *q;
+    v.x = p.alpha * v.x + bb.x; v.y = p.alpha * v.y + bb.y; v.z = p.alpha * v.z + bb.z; v.w = p.alpha * v.w + bb.w;
+    *q = v;
+    if (m0 + row < p.M) { s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+  }
+  s = bn_colreduce(s, red, et);
+  const float icnt = cnt_i > 0 ? 1.f / cnt : 0.f;
+  const float4 mean_loc = make_float4(s.x * icnt, s.y * icnt, s.z * icnt, s.w * icnt);
+  // ---- pass B: local M2 = sum (v - mean_loc)^2
+  float4 q2 = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int j = 0; j < nj; ++j) {
+    const int row = row0 + g + 8 * j;
+    if (m0 + row < p.M) {
+      const float4 v = *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4);
+      const float dx = v.x - mean_loc.x, dy = v.y - mean_loc.y, dz = v.z - mean_loc.z, dw = v.w - mean_loc.w;
+      q2.x += dx * dx; q2.y += dy * dy; q2.z += dz * dz; q2.w += dw * dw;
+    }
+  }
+  q2 = bn_colreduce(q2, red + 4 * BN, et);
+  const int nct = CY * S;
+  float4 mu = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 pm[8], pq[8];
+  float pc[8];
+  if (stat_recv != nullptr) {
+    // ---- push: store my (count, mean, M2) into slot `me` of every cluster CTA's statistics buffer
+    // (st.async signals that CTA's stat_bar), then wait for all nct slots of my own buffer
+    const int me = y + CY * r;
+    if (g == 0) {
+      const float4 cc = make_float4(cnt, cnt, cnt, cnt);
+      const uint32_t slot = stat_recv_u32 + (uint32_t)((me * 3 * BN + c4 * 4) * 4);
+      for (int c = 0; c < nct; ++c) {
+        const uint32_t rb = map_cluster(stat_bar, c);
+        st_async_v4(map_cluster(slot, c), cc, rb);
+        st_async_v4(map_cluster(slot + BN * 4, c), mean_loc, rb);
+        st_async_v4(map_cluster(slot + 2 * BN * 4, c), q2, rb);
+      }
+    }
+    mbar_wait(stat_bar, 0);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      pc[c] = 0.f; pm[c] = make_float4(0.f, 0.f, 0.f, 0.f); pq[c] = pm[c];
+      if (c < nct) {
+        const float* sl = stat_recv + c * 3 * BN + c4 * 4;
+        pc[c] = sl[0];
+        pm[c] = *reinterpret_cast<const float4*>(sl + BN);
+        pq[c] = *reinterpret_cast<const float4*>(sl + 2 * BN);
+        mu.x += pc[c] * pm[c].x; mu.y += pc[c] * pm[c].y; mu.z += pc[c] * pm[c].z; mu.w += pc[c] * pm[c].w;
+      }
+    }
+  } else {
+  if (g == 0) {
+    *reinterpret_cast<float4*>(stat + 0 * BN + c4 * 4) = make_float4(cnt, cnt, cnt, cnt);
+    *reinterpret_cast<float4*>(stat + 1 * BN + c4 * 4) = mean_loc;
+    *reinterpret_cast<float4*>(stat + 2 * BN + c4 * 4) = q2;
+  }
+  // ---- publish, then merge the statistics of every CTA of the cluster (same order everywhere)
+  __syncwarp();
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  const uint32_t stat_u32 = base_u32 + BN_STAT_OFF + BN_RED_FLOATS * 4 + c4 * 16;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    pc[c] = 0.f; pm[c] = make_float4(0.f, 0.f, 0.f, 0.f); pq[c] = pm[c];
+    if (c < nct) {
+      uint32_t remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(stat_u32), "r"(c));
+      float4 cc;
+      asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(cc.x), "=f"(cc.y), "=f"(cc.z), "=f"(cc.w) : "r"(remote) : "memory");
+      asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(pm[c].x), "=f"(pm[c].y), "=f"(pm[c].z), "=f"(pm[c].w) : "r"(remote + BN * 4) : "memory");
+      asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(pq[c].x), "=f"(pq[c].y), "=f"(pq[c].z), "=f"(pq[c].w) : "r"(remote + 2 * BN * 4) : "memory");
+      pc[c] = cc.x;
+      mu.x += cc.x * pm[c].x; mu.y += cc.x * pm[c].y; mu.z += cc.x * pm[c].z; mu.w += cc.x * pm[c].w;
+    }
+  }
+  }
+  const float invM = 1.f / (float)p.M;
+  mu.x *= invM; mu.y *= invM; mu.z *= invM; mu.w *= invM;
+  float4 var = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    if (c < nct) {
+      const float dx = pm[c].x - mu.x, dy = pm[c].y - mu.y, dz = pm[c].z - mu.z, dw = pm[c].w - mu.w;
+      var.x += pq[c].x + pc[c] * dx * dx; var.y += pq[c].y + pc[c] * dy * dy;
+      var.z += pq[c].z + pc[c] * dz * dz; var.w += pq[c].w + pc[c] * dw * dw;
+    }
+  }
+  var.x *= invM; var.y *= invM; var.z *= invM; var.w *= invM;                 // biased (normalisation)
+  const float4 inv = make_float4(rsqrtf(var.x + bn.eps), rsqrtf(var.y + bn.eps), rsqrtf(var.z + bn.eps), rsqrtf(var.w + bn.eps));
+  float ga[4], be[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    ga[e] = n + e < p.N ? __ldg(bn.gamma + n + e) : 0.f;
+    be[e] = n + e < p.N ? __ldg(bn.beta + n + e) : 0.f;
+  }
+  if (y == 0 && r == 0 && g == 0) {
+    const float unb = (float)p.M / (float)(p.M > 1 ? p.M - 1 : 1);
+    const float mus[4] = {mu.x, mu.y, mu.z, mu.w}, vars[4] = {var.x, var.y, var.z, var.w},
+                invs[4] = {inv.x, inv.y, inv.z, inv.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      if (n + e < p.N) {
+        bn.running_mean[n + e] = (1.f - bn.momentum) * bn.running_mean[n + e] + bn.momentum * mus[e];
+        bn.running_var[n + e] = (1.f - bn.momentum) * bn.running_var[n + e] + bn.momentum * vars[e] * unb;
+        if (bn.save_mean) { bn.save_mean[n + e] = mus[e]; bn.save_invstd[n + e] = invs[e]; }
+      }
+    }
+    if (blockIdx.x == 0 && et == 0 && bn.nbt) bn.nbt[0] += 1.f;
+  }
+  // ---- normalise own slice: pre-activation -> p.d, relu(bn) -> bn.out (column window of the wide buffer)
+  const bool vec = vec_ok && (n + 3 < p.N);
+  for (int j = 0; j < nj; ++j) {
+    const int row = row0 + g + 8 * j;
+    const int m = m0 + row;
+    if (m >= p.M || n >= p.N) continue;
+    const float4 v = *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4);
+    float4 o;
+    o.x = fmaxf((v.x - mu.x) * inv.x * ga[0] + be[0], 0.f); o.y = fmaxf((v.y - mu.y) * inv.y * ga[1] + be[1], 0.f);
+    o.z = fmaxf((v.z - mu.z) * inv.z * ga[2] + be[2], 0.f); o.w = fmaxf((v.w - mu.w) * inv.w * ga[3] + be[3], 0.f);
+    if (vec) {
+      *reinterpret_cast<float4*>(p.d + (size_t)m * p.ldd + n) = v;
+      *reinterpret_cast<float4*>(bn.out + (size_t)m * bn.ldo + n) = o;
+    } else {
+      const float vs[4] = {v.x, v.y, v.z, v.w}, os[4] = {o.x, o.y, o.z, o.w};
+      for (int e = 0; e < 4 && n + e < p.N; ++e) {
+        p.d[(size_t)m * p.ldd + n + e] = vs[e];
+        bn.out[(size_t)m * bn.ldo + n + e] = os[e];
+      }
+    }
+  }
+}
+
 // Optional in-kernel timeline of CTA (0,0,0) (clock64 at phase boundaries) for latency analysis.
 __device__ long long g_gemm_timeline[16];
 __device__ int g_gemm_timeline_on = 0;
@@ -214,7 +433,7 @@ template <bool A_MN, bool B_MN, int EPI, bool X3>
 __global__ void __maxnreg__(112)
 k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
           const ftg_gemm_args p, int split_k, float* __restrict__ workspace, int* __restrict__ tile_counters,
-          int vec_ok_i, int cluster_mode, int STAGES) {
+          int vec_ok_i, int cluster_mode, int STAGES, const ftg_bn_args bn) {
   const bool vec_ok = vec_ok_i != 0;
   constexpr int STG = X3 ? 2 * STAGE_BYTES : STAGE_BYTES;   // fp32x3: [A_hi | B_hi | A_lo | B_lo] per stage
   extern __shared__ unsigned char smem_raw[];
@@ -228,6 +447,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
   const uint32_t tmem_full_bar = bars + 8u * (2 * STAGES);
   auto split_bar = [&](int s) { return bars + 8u * (2 * STAGES + 3 + s); };   // hi/lo copies of stage s are ready
+  // push-based cluster reduction (cluster_mode == 2): peers store their partial of MY slice into `recv`
+  // (st.async) and signal recv_bar; BatchNorm statistics of all cluster CTAs land in `stat_recv` / stat_bar
+  const uint32_t recv_bar = bars + 8u * (3 * STAGES + 3), stat_bar = bars + 8u * (3 * STAGES + 4);
+  const uint32_t recv_u32 = bars + 256u, stat_recv_u32 = recv_u32 + RECV_BYTES;
+  float* recv = reinterpret_cast<float*>(gen_base + STAGES * STG + 256);
+  float* stat_recv = reinterpret_cast<float*>(gen_base + STAGES * STG + 256 + RECV_BYTES);
+  const bool push = cluster_mode == 2;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM, z = blockIdx.z;
@@ -242,6 +468,14 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     if (X3) for (int s = 0; s < STAGES; ++s) mbar_init(split_bar(s), 4);      // one arrival per splitter warp
     mbar_init(tmem_full_bar, 1);
+    if (push) {
+      // one arrival (this thread) + the bytes the peers will push: (S-1) slices of BM/S rows x 64 floats,
+      // and for the BatchNorm epilogue 768 B of statistics from each of the CY*S cluster CTAs (self included)
+      mbar_init(recv_bar, 1);
+      mbar_init(stat_bar, 1);
+      mbar_expect_tx(recv_bar, (uint32_t)((split_k - 1) * (BM / split_k) * BN * 4));
+      if (EPI == EPI_BN) mbar_expect_tx(stat_bar, (uint32_t)(split_k * (int)gridDim.y * 3 * BN * 4));
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -256,6 +490,10 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  // push protocol: tell the cluster that this CTA's receive barriers exist (non-blocking; the matching
+  // wait sits right before the first remote store, a whole main loop later)
+  // (.relaxed: fence.mbarrier_init.release.cluster above already publishes the initialised barriers)
+  if (push) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");        // predecessor's outputs are visible from here on
 
   if (warp == 0 && lane == 0) {
@@ -325,6 +563,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     const int q = warp & 3;                      // TMEM lane quadrant owned by this warp
     const int row_in_tile = q * 32 + lane;
     const int m = m0 + row_in_tile;
+    if (push) asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");   // peers' receive barriers exist
     if (X3) {
       // ---- fp32x3 splitter: as each stage lands, rewrite it as hi (in place) + lo (upper half of the stage)
       const int st = threadIdx.x - 64;
@@ -338,13 +577,26 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         float4 v[PER];
 #pragma unroll
         for (int i = 0; i < PER; ++i) v[i] = hi4[i * 128 + st];
+        if (p.x3 == 2) {
+          // The tensor core reads an fp32 word as tf32 by dropping its 13 low mantissa bits, so the
+          // stage as TMA wrote it already IS the hi operand; only lo = rna_tf32(x - trunc_tf32(x))
+          // has to be written (one third less shared-memory traffic per stage).
 #pragma unroll
-        for (int i = 0; i < PER; ++i) {
-          float4 h, l;
-          split_tf32(v[i].x, h.x, l.x); split_tf32(v[i].y, h.y, l.y);
-          split_tf32(v[i].z, h.z, l.z); split_tf32(v[i].w, h.w, l.w);
-          hi4[i * 128 + st] = h;
-          lo4[i * 128 + st] = l;
+          for (int i = 0; i < PER; ++i) {
+            float4 l;
+            l.x = lo_trunc_tf32(v[i].x); l.y = lo_trunc_tf32(v[i].y);
+            l.z = lo_trunc_tf32(v[i].z); l.w = lo_trunc_tf32(v[i].w);
+            lo4[i * 128 + st] = l;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < PER; ++i) {
+            float4 h, l;
+            split_tf32(v[i].x, h.x, l.x); split_tf32(v[i].y, h.y, l.y);
+            split_tf32(v[i].z, h.z, l.z); split_tf32(v[i].w, h.w, l.w);
+            hi4[i * 128 + st] = h;
+            lo4[i * 128 + st] = l;
+          }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
         __syncwarp();
@@ -423,8 +675,76 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     if (threadIdx.x == 64) TL(8);
     (void)m;
   }
-  if (cluster_mode) {
-    // ---- split-K inside a thread-block cluster (cluster = the split_k CTAs of one output tile):
+  if (push) {
+    // ---- split-K inside a thread-block cluster, PUSH protocol (FTG_CLUSTER_PUSH=1; alternative to pull).  Every CTA has staged its
+    // partial tile in its own shared memory.  CTA r owns rows [r*BM/S, (r+1)*BM/S) of the tile: each
+    // CTA stores the other ranks' slices of its partial straight into the owners' receive buffers with
+    // st.async (the store signals the owner's mbarrier when it lands), then waits on its OWN barrier
+    // for the S-1 inbound slices, sums them in rank order (deterministic) and runs the fused epilogue
+    // on its slice.  The data hand-off needs no cluster-wide barrier and no remote loads: one one-way
+    // DSMEM trip instead of barrier + round trip + barrier (see profiles/gemm_timeline.json).
+    const int S = split_k, r = z;
+    const int CY = (EPI == EPI_BN) ? (int)gridDim.y : 1;    // cluster = (1, CY, S); ctarank(y', z') = y' + CY * z'
+    const int ybase = (EPI == EPI_BN) ? (int)blockIdx.y : 0;
+    // (phase-1 wait -- "every peer's receive barriers exist" -- of the epilogue warps sits at the start of their
+    // role, hidden under the main loop; the producer / issuer warps take theirs here, after their work)
+    if (warp < 2) {
+      __syncwarp();
+      asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
+    if (threadIdx.x == 64) TL(10);
+    if (warp >= 2) {
+      const int et = threadIdx.x - 64;
+      float* stage = reinterpret_cast<float*>(gen_base);
+      const int log2S = 31 - __clz(S);
+      const int cpr = (BM * BN / 4) / S;                   // float4 chunks per rank slice
+      const int R = BM / S;
+      // push: chunk t of the other ranks' slices (t enumerates (owner o != r, j))
+      if (S > 1) {
+#pragma unroll
+        for (int t = 0; t < CHUNKS; ++t) {
+          const int j = t >> log2S, o = t & (S - 1);
+          if (o == r) continue;
+          const int f = o * cpr + j * 128 + et;
+          const int row = f >> 4, c4 = f & 15;
+          const float4 v = *reinterpret_cast<const float4*>(stage + row * SLD + c4 * 4);
+          const uint32_t dst_local = recv_u32 + (uint32_t)(((r * R + (row - o * R)) * BN + c4 * 4) * 4);
+          st_async_v4(map_cluster(dst_local, ybase + CY * o), v, map_cluster(recv_bar, ybase + CY * o));
+        }
+      }
+      if (S > 1) mbar_wait(recv_bar, 0);                                       // my inbound slices have landed
+      if (threadIdx.x == 64) TL(11);
+      // own slice: sum the S partials in rank order
+#pragma unroll
+      for (int j = 0; j < CHUNKS; ++j) {
+        if (j < (CHUNKS >> log2S)) {
+          const int f = r * cpr + j * 128 + et;
+          const int row = f >> 4, c4 = f & 15;
+          float4* own = reinterpret_cast<float4*>(stage + row * SLD + c4 * 4);
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int q = 0; q < S; ++q) {
+            const float4 v = (q == r) ? *own
+                                      : *reinterpret_cast<const float4*>(recv + (q * R + (row - r * R)) * BN + c4 * 4);
+            if (q == 0) acc = v;
+            else { acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w; }
+          }
+          *own = acc;
+        }
+      }
+      if (EPI == EPI_BN) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        bn_epilogue(p, bn, vec_ok, gen_base, base, et, m0, n0, r, S, CY, (int)blockIdx.y, stat_recv, stat_recv_u32, stat_bar);
+      } else {
+        epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0, r * cpr, CHUNKS / S);
+      }
+      if (threadIdx.x == 64) TL(12);
+    }
+    // nobody leaves while a peer may still have stores to this CTA un-issued (arrive only after the epilogue:
+    // a release-arrive in the middle would stall on the outbound stores)
+    __syncwarp();
+    asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
+  } else if (cluster_mode) {
+    // ---- split-K inside a thread-block cluster, PULL protocol (default):
     // every CTA has staged its partial tile in its own shared memory; after a cluster barrier
     // CTA r sums slice r of all partials through distributed shared memory (fixed rank order:
     // deterministic), applies the fused epilogue to that slice and stores it.  No global
@@ -436,7 +756,11 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       const int et = threadIdx.x - 64;
       float* stage = reinterpret_cast<float*>(gen_base);
       const uint32_t stage_u32 = base;
-      const int S = split_k, r = z;                        // cluster spans grid.z: rank == z
+      const int S = split_k, r = z;                        // split-K rank inside the cluster
+      // cluster = (1, CY, S): CY = all M-tiles of the panel for the BatchNorm epilogue, else 1;
+      // %cluster_ctarank of CTA (y', z') is y' + CY * z'
+      const int CY = (EPI == EPI_BN) ? (int)gridDim.y : 1;
+      const int ybase = (EPI == EPI_BN) ? (int)blockIdx.y : 0;
       const int log2S = 31 - __clz(S);
       const int cpr = (BM * BN / 4) / S;                   // chunks per rank
       float4 v[CHUNKS];
@@ -448,7 +772,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         v[t] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (m0 + (f >> 4) < p.M) {                           // rows past M carry nothing: skip their DSMEM traffic
           uint32_t remote;
-          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(q));
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(ybase + CY * q));
           asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
                        : "=f"(v[t].x), "=f"(v[t].y), "=f"(v[t].z), "=f"(v[t].w) : "r"(remote) : "memory");
         }
@@ -465,8 +789,17 @@ k_gemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         }
       }
       if (threadIdx.x == 64) TL(11);
-      epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0, r * cpr, CHUNKS / S);
+      if (EPI == EPI_BN) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");     // own slice fully reduced in shared memory
+        bn_epilogue(p, bn, vec_ok, gen_base, base, et, m0, n0, r, S, CY, (int)blockIdx.y, nullptr, 0u, 0u);
+      } else {
+        epilogue_tile<EPI>(p, vec_ok, stage, et, m0, n0, r * cpr, CHUNKS / S);
+      }
       if (threadIdx.x == 64) TL(12);
+    } else if (EPI == EPI_BN) {
+      // warps 0/1 take part in the statistics exchange barrier of bn_epilogue (.aligned: all threads)
+      __syncwarp();
+      asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     }
     // peers may still be reading this CTA's shared memory: nobody leaves before everybody is done
     __syncwarp();
@@ -712,6 +1045,19 @@ int choose_stages(long long ctas, int kblocks_per_cta, int cluster_size, bool x3
   return s < 2 ? 2 : s;
 }
 
+// Cluster split-K reduction protocol: pull (remote loads between two cluster barriers, default) or push
+// (st.async into the owner's receive buffer, FTG_CLUSTER_PUSH=1).  Measured on B200 (profiles/gemm_cluster_protocols.md):
+// a cluster barrier costs 1-2 k cycles and moving a 32 KB tile through DSMEM ~2 k cycles either way, so the two
+// protocols finish within 2 % of each other per GEMM and the whole iteration is not faster with push.
+int g_cluster_push = -1;
+bool use_push() {
+  if (g_cluster_push < 0) {
+    const char* e = getenv("FTG_CLUSTER_PUSH");
+    g_cluster_push = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return g_cluster_push == 1;
+}
+
 // Persistent-tile variant: opt-in (experimental).
 int g_persistent = -1;
 bool use_persistent() {
@@ -724,9 +1070,13 @@ bool use_persistent() {
 
 template <bool A_MN, bool B_MN, int EPI, bool X3 = false>
 int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
-               int vec_ok, cudaStream_t stream) {
-  if (!X3 && p.x3) return launch_epi<A_MN, B_MN, EPI, true>(ma, mb, p, split_k, ws, ctr, vec_ok, stream);
-  const int cluster_mode = (ws == nullptr && split_k > 1) ? 1 : 0;   // no workspace given: reduce through DSMEM
+               int vec_ok, cudaStream_t stream, const ftg_bn_args* bnp = nullptr) {
+  if (!X3 && p.x3) return launch_epi<A_MN, B_MN, EPI, true>(ma, mb, p, split_k, ws, ctr, vec_ok, stream, bnp);
+  // no workspace given: reduce through DSMEM; the BatchNorm epilogue always runs as a cluster
+  // 2 = push protocol (st.async into the slice owner's shared memory, default), 1 = pull (FTG_CLUSTER_PUSH=0)
+  const int cluster_mode = ((ws == nullptr && split_k > 1) || EPI == EPI_BN) ? (use_push() ? 2 : 1) : 0;
+  ftg_bn_args bn = {};
+  if (bnp) bn = *bnp;
   // function attributes are per device: one flag per (instantiation, device)
   static std::atomic<bool> attr_done_dev[64];
   int dev_id = 0;
@@ -734,7 +1084,10 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
   std::atomic<bool>& attr_done = attr_done_dev[dev_id];
   if (!attr_done.load(std::memory_order_acquire)) {
     cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         X3 ? smem_bytes(MAX_STAGES_X3, true) : SMEM_BYTES);
+                                         X3 ? (smem_bytes(MAX_STAGES_X3, true) > smem_bytes(MAX_STAGES_X3 - 1, true, true)
+                                                   ? smem_bytes(MAX_STAGES_X3, true)
+                                                   : smem_bytes(MAX_STAGES_X3 - 1, true, true))
+                                            : smem_bytes(MAX_STAGES, false, true));
     if (e != cudaSuccess) return (int)e;
     e = cudaFuncSetAttribute(k_gemm_tc<A_MN, B_MN, EPI, X3>, cudaFuncAttributePreferredSharedMemoryCarveout,
                              cudaSharedmemCarveoutMaxShared);
@@ -742,7 +1095,7 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
     attr_done.store(true, std::memory_order_release);
   }
   dim3 grid(ftg_cdiv(p.N, BN), ftg_cdiv(p.M, BM), split_k);
-  if (!X3 && use_persistent() && split_k == 1 && (long long)grid.x * grid.y > 148) {
+  if (!X3 && EPI != EPI_BN && use_persistent() && split_k == 1 && (long long)grid.x * grid.y > 148) {
     static std::atomic<bool> pattr_done_dev[64];
     if (!pattr_done_dev[dev_id].load(std::memory_order_acquire)) {
       cudaError_t e = cudaFuncSetAttribute(k_gemm_tc_persist<A_MN, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -763,20 +1116,22 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
     pc.numAttrs = g_ftg_pdl ? 1 : 0;
     return (int)cudaLaunchKernelEx(&pc, k_gemm_tc_persist<A_MN, B_MN, EPI>, ma, mb, p, vec_ok, (int)grid.y, (int)grid.x);
   }
-  const int stages = choose_stages((long long)grid.x * grid.y * grid.z, (ftg_cdiv(p.K, BK) + split_k - 1) / split_k,
-                                   cluster_mode ? split_k : 1, X3);
+  const int cluster_ctas = cluster_mode ? split_k * (EPI == EPI_BN ? (int)grid.y : 1) : 1;
+  int stages = choose_stages((long long)grid.x * grid.y * grid.z, (ftg_cdiv(p.K, BK) + split_k - 1) / split_k,
+                             cluster_ctas, X3);
+  if (X3 && cluster_mode == 2 && stages > MAX_STAGES_X3 - 1) stages = MAX_STAGES_X3 - 1;   // room for the receive buffers
   ++g_ftg_launch_count;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = smem_bytes(stages, X3);
+  cfg.dynamicSmemBytes = smem_bytes(stages, X3, cluster_mode == 2);
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
   if (cluster_mode) {
     attr[na].id = cudaLaunchAttributeClusterDimension;
     attr[na].val.clusterDim.x = 1;
-    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.y = (EPI == EPI_BN) ? grid.y : 1;
     attr[na].val.clusterDim.z = (unsigned)split_k;
     ++na;
   }
@@ -788,15 +1143,19 @@ int launch_epi(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args
   cfg.attrs = attr;
   cfg.numAttrs = na;
   return (int)cudaLaunchKernelEx(&cfg, k_gemm_tc<A_MN, B_MN, EPI, X3>, ma, mb, p, split_k, ws, ctr, vec_ok,
-                                 cluster_mode, stages);
+                                 cluster_mode, stages, bn);
 }
 
 template <bool A_MN, bool B_MN>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const ftg_gemm_args& p, int split_k, float* ws, int* ctr,
-           cudaStream_t stream) {
+           cudaStream_t stream, const ftg_bn_args* bn = nullptr) {
   auto al = [](const void* ptr, int ld) { return ptr == nullptr || (((reinterpret_cast<uintptr_t>(ptr) & 15) == 0) && (ld & 3) == 0); };
   const int vec_ok = al(p.d, p.ldd) && al(p.mask_in, p.ld_mask_in) && al(p.mask_out, p.ld_mask_out) &&
                      al(p.drop_u, p.ld_drop_u) && al(p.bias, 0);
+  if (bn) {
+    const int ok = al(p.d, p.ldd) && al(bn->out, bn->ldo) && al(p.bias, 0) && al(bn->gamma, 0) && al(bn->beta, 0);
+    return launch_epi<A_MN, B_MN, EPI_BN>(ma, mb, p, split_k, nullptr, nullptr, ok, stream, bn);
+  }
   // pick the epilogue specialisation that matches the flag combination exactly
   int epi = EPI_GENERIC;
   const bool b = p.bias != nullptr, a = p.act != 0, mi = p.mask_in != nullptr, acc = p.accumulate != 0;
@@ -858,6 +1217,12 @@ extern "C" int ftg_gemm_tc_set_persistent(int on) {
   return 0;
 }
 
+// 1: push protocol for the in-cluster split-K reduction, 0: pull protocol (default).
+extern "C" int ftg_gemm_tc_set_cluster_push(int on) {
+  g_cluster_push = on ? 1 : 0;
+  return 0;
+}
+
 extern "C" int ftg_gemm_tc_choose_cluster_split(int M, int N, int K) {
   int tiles = ftg_gemm_tc_num_tiles(M, N);
   int nkb = ftg_cdiv(K, BK);
@@ -891,6 +1256,44 @@ extern "C" int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* worksp
                           : launch<true, false>(ma, mb, p, split_k, workspace, tile_counters, s);
   return p.b_t ? launch<false, true>(ma, mb, p, split_k, workspace, tile_counters, s)
                : launch<false, false>(ma, mb, p, split_k, workspace, tile_counters, s);
+}
+
+// Linear + BatchNorm1d(train) + ReLU + concat-store in one launch (EPI_BN, see bn_epilogue).
+// Returns FTG_ERR_UNSUPPORTED when the shape does not fit one cluster per column panel
+// (more than 4 M-tiles, i.e. batch > 512) or an epilogue flag other than bias is set: the caller then
+// runs ftg_gemm_tc + ftg_bn_relu_fwd.
+extern "C" int ftg_gemm_tc_bn_plan(int M, int K) {
+  const int cy = ftg_cdiv(M, BM), nkb = ftg_cdiv(K, BK);
+  if (cy < 1 || cy > 4) return 0;
+  static int cap = -1;
+  if (cap < 0) {
+    const char* e = getenv("FTG_BN_SPLIT");       // experiments: largest split-K factor of the fused-BN GEMM
+    cap = e ? atoi(e) : 8;
+    if (cap < 1) cap = 1;
+  }
+  int s = 1;
+  while (cy * s * 2 <= 8 && s * 2 <= cap && nkb / (s * 2) >= 2) s *= 2;
+  return s;
+}
+
+extern "C" int ftg_gemm_tc_bn(const ftg_gemm_args* args, const ftg_bn_args* bn, ftg_stream_t stream) {
+  const ftg_gemm_args& p = *args;
+  if (!bn || !bn->gamma || !bn->beta || !bn->running_mean || !bn->running_var || !bn->out) return FTG_ERR_UNSUPPORTED;
+  if (p.M <= 0 || p.N <= 0 || p.K <= 0) return FTG_ERR_UNSUPPORTED;
+  if (p.act || p.mask_in || p.mask_out || p.accumulate) return FTG_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(p.a) & 15) || (reinterpret_cast<uintptr_t>(p.b) & 15) || (p.lda & 3) || (p.ldb & 3))
+    return FTG_ERR_UNSUPPORTED;
+  const int split_k = ftg_gemm_tc_bn_plan(p.M, p.K);
+  if (split_k < 1) return FTG_ERR_UNSUPPORTED;
+  CUtensorMap ma, mb;
+  bool ok = p.a_t ? make_map(&ma, p.a, p.M, p.K, p.lda, 32, BK, true) : make_map(&ma, p.a, p.K, p.M, p.lda, BK, BM, false);
+  ok = ok && (p.b_t ? make_map(&mb, p.b, p.N, p.K, p.ldb, 32, BK, true) : make_map(&mb, p.b, p.K, p.N, p.ldb, BK, BN, false));
+  if (!ok) return FTG_ERR_UNSUPPORTED;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (p.a_t) return p.b_t ? launch<true, true>(ma, mb, p, split_k, nullptr, nullptr, s, bn)
+                          : launch<true, false>(ma, mb, p, split_k, nullptr, nullptr, s, bn);
+  return p.b_t ? launch<false, true>(ma, mb, p, split_k, nullptr, nullptr, s, bn)
+               : launch<false, false>(ma, mb, p, split_k, nullptr, nullptr, s, bn);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -230,6 +230,15 @@ class TrainEngine:
         L = len(self.gh)
         for l in range(1, L + 1):
             x = h[:, self.off[l - 1]: self.off[0] + self.d0]
+            if training:
+                # Linear + BatchNorm(batch stats) + ReLU + concat-store: one launch (GEMM epilogue)
+                ops.linear_bn_relu(
+                    x, self._gw(l - 1), a[l - 1], h[:, self.off[l]: self.off[l - 1]],
+                    bias=self._g(l - 1, "fc.bias"), gamma=self._g(l - 1, "bn.weight"), beta=self._g(l - 1, "bn.bias"),
+                    running_mean=self._g(l - 1, "bn.running_mean"), running_var=self._g(l - 1, "bn.running_var"),
+                    save_mean=self.save_mean[l - 1], save_invstd=self.save_invstd[l - 1], eps=self.cfg.bn_eps,
+                    momentum=self.cfg.bn_momentum, num_batches_tracked=self._g(l - 1, "bn.num_batches_tracked"))
+                continue
             ops.linear(x, self._gw(l - 1), a[l - 1], bias=self._g(l - 1, "fc.bias"))
             ops.bn_relu_fwd(
                 a[l - 1], self._g(l - 1, "bn.weight"), self._g(l - 1, "bn.bias"),

@@ -157,6 +157,7 @@ def fit_vbgmm_1d(
     reg_covar: float = 1e-6,
     device=None,
     use_kernel: bool = True,
+    init_centers=None,
 ):
     """Fit DP-GMMs to every row of ``x`` (``[C, n]``: C columns, n samples) at once.
 
@@ -169,7 +170,7 @@ def fit_vbgmm_1d(
         x = x[None, :]
     dev = torch.device(device) if device is not None else x.device
     if dev.type == "cuda" and n_components <= 12 and use_kernel:
-        fitted = _fit_vbgmm_kernel(x.to(dev), n_components, dp_prior, max_iter, tol, reg_covar)
+        fitted = _fit_vbgmm_kernel(x.to(dev), n_components, dp_prior, max_iter, tol, reg_covar, init_centers)
         if fitted is not None:
             return fitted
     x = x.to(device=dev, dtype=torch.float64)
@@ -242,17 +243,17 @@ def fit_vbgmm_1d(
     return out
 
 
-def _fit_vbgmm_kernel(x, K, dp_prior, max_iter, tol, reg_covar):
-    """One CTA per column on the device (``csrc/vbgmm.cu``); ``None`` if the native library is missing."""
+def _fit_vbgmm_kernel(x, K, dp_prior, max_iter, tol, reg_covar, init_centers=None):
+    """One CTA per column on the device (``csrc/vbgmm.cu``); ``None`` if the native library is missing.
+    ``init_centers`` ([C, K] quantile seeds, e.g. from the fused statistics kernel) avoids sorting here."""
     try:
         from ..ops import native
     except Exception:
         return None
     xf = x.to(torch.float32).contiguous()
-    srt = torch.sort(xf, dim=1).values
-    n = xf.shape[1]
-    q = ((torch.arange(K, device=xf.device, dtype=torch.float64) + 0.5) / K * (n - 1)).round().long()
-    out, _ = native.vbgmm_fit(xf, srt[:, q], dp_prior, max_iter, tol, reg_covar)
+    if init_centers is None:
+        init_centers = native.quantile_centers(xf, K)
+    out, _ = native.vbgmm_fit(xf, init_centers, dp_prior, max_iter, tol, reg_covar)
     arr = out.cpu().numpy()
     return [GMMParams.from_array(arr[c]) for c in range(arr.shape[0])]
 

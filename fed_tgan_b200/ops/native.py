@@ -46,6 +46,14 @@ class GemmArgs(C.Structure):
     ]
 
 
+class BnArgs(C.Structure):
+    _fields_ = [
+        ("gamma", _vp), ("beta", _vp), ("running_mean", _vp), ("running_var", _vp),
+        ("save_mean", _vp), ("save_invstd", _vp), ("out", _vp), ("ldo", _i),
+        ("eps", _f), ("momentum", _f), ("nbt", _vp),
+    ]
+
+
 def _sig(name, argtypes, restype=_i):
     fn = getattr(lib, name)
     fn.argtypes = argtypes
@@ -55,6 +63,8 @@ def _sig(name, argtypes, restype=_i):
 
 _gemm_simt = _sig("ftg_gemm_simt", [C.POINTER(GemmArgs), _vp])
 _gemm_tc = _sig("ftg_gemm_tc", [C.POINTER(GemmArgs), _i, _vp, _vp, _vp])
+_gemm_tc_bn = _sig("ftg_gemm_tc_bn", [C.POINTER(GemmArgs), C.POINTER(BnArgs), _vp])
+_gemm_tc_bn_plan = _sig("ftg_gemm_tc_bn_plan", [_i, _i])
 _choose_split = _sig("ftg_gemm_tc_choose_split", [_i, _i, _i])
 _choose_cluster_split = _sig("ftg_gemm_tc_choose_cluster_split", [_i, _i, _i])
 _ws_bytes = _sig("ftg_gemm_tc_workspace_bytes", [_i, _i, _i], _ll)
@@ -98,6 +108,10 @@ _symm_free = _sig("ftg_symm_free", [_vp])
 _symm_export = _sig("ftg_symm_export", [_vp, C.c_char_p])
 _symm_open = _sig("ftg_symm_open", [C.c_char_p, C.POINTER(_vp)])
 _symm_close = _sig("ftg_symm_close", [_vp])
+_sort_pad = _sig("ftg_sort_pad", [_i])
+_gmm_sample_sort = _sig("ftg_gmm_sample_sort", [_vp, _i, _i, _i, C.c_ulonglong, _i, _vp, _vp])
+_sort_rows = _sig("ftg_sort_rows", [_vp, _i, _i, _vp, _vp])
+_fed_stats = _sig("ftg_fed_stats_to_weights", [_vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp])
 _stats = _sig("ftg_stats_to_weights", [_vp, _i, _i, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp])
 _vbgmm = _sig("ftg_vbgmm_fit", [_vp, _i, _i, _vp, _i, C.c_double, _i, C.c_double, C.c_double, _i, _vp, _vp, _vp])
 _launch_count = _sig("ftg_last_launch_count", [], _ll)
@@ -147,6 +161,7 @@ def _ld(t):
 #           products);  "fp32": exact fp32 on the CUDA cores (k_gemm_simt, the oracle / fallback).
 PRECISIONS = ("fp32x3", "tf32", "fp32")
 _precision = os.environ.get("FEDTGAN_PRECISION", "fp32x3")
+_x3_mode = int(os.environ.get("FEDTGAN_X3_MODE", "1"))    # 1: write hi and lo copies; 2: lo only (hi = hardware truncation)
 _simt_fallbacks = 0          # tensor-core launches that fell back to k_gemm_simt (unaligned operands)
 _splitk_mode = os.environ.get("FEDTGAN_SPLITK", "cluster")     # "cluster" (DSMEM) | "workspace"
 _scratch = {}
@@ -161,6 +176,14 @@ def set_precision(p: str):
 
 def get_precision() -> str:
     return _precision
+
+
+def set_x3_mode(mode: int):
+    """fp32x3 splitter variant: 1 = rewrite the stage as rna_tf32 hi + lo copy, 2 = keep the stage as the
+    hi operand (the tensor core truncates fp32 words to tf32) and write only the lo copy."""
+    global _x3_mode
+    assert mode in (1, 2)
+    _x3_mode = mode
 
 
 def simt_fallback_count() -> int:
@@ -218,7 +241,7 @@ def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None
     prec = precision or _precision
     st = _stream()
     if prec in ("tf32", "fp32x3"):
-        g.x3 = 1 if prec == "fp32x3" else 0
+        g.x3 = _x3_mode if prec == "fp32x3" else 0
         ws = ctr = None
         if split_k is None and splitk_mode == "cluster":
             sk = _choose_cluster_split(g.M, g.N, g.K)        # DSMEM reduction inside a cluster: no scratch
@@ -248,9 +271,50 @@ def linear(a, b, out, *, a_t=False, b_t=False, bias=None, act=None, mask_in=None
     return out
 
 
+_fused_bn = os.environ.get("FEDTGAN_FUSED_BN", "1") != "0"
+
+
+def linear_bn_relu(x, w, a_out, out, *, bias, gamma, beta, running_mean, running_var, save_mean=None, save_invstd=None,
+                   eps=1e-5, momentum=0.1, num_batches_tracked=None, precision=None):
+    """Residual block forward: ``a_out = x @ w.T + bias`` and ``out = relu(batchnorm_train(a_out))`` (``out`` may be a
+    column window of a wider buffer).  One tcgen05 launch with the batch statistics reduced inside a thread-block
+    cluster (``ftg_gemm_tc_bn``) when the shape allows it (batch <= 512, tensor-core precision); otherwise the GEMM
+    followed by ``bn_relu_fwd``.  Reference: ``Residual.forward``, ``ctgan.py:40-44``."""
+    prec = precision or _precision
+    if _fused_bn and prec in ("tf32", "fp32x3") and _gemm_tc_bn_plan(a_out.shape[0], x.shape[1]) > 0:
+        g = _gemm_args(x, w, a_out, False, False, bias, None, None, None, None, None, 0, False, 1.0, 0.2, 0.5)
+        g.x3 = _x3_mode if prec == "fp32x3" else 0
+        b = BnArgs()
+        b.gamma, b.beta = _p(gamma), _p(beta)
+        b.running_mean, b.running_var = _p(running_mean), _p(running_var)
+        b.save_mean, b.save_invstd = _p(save_mean), _p(save_invstd)
+        b.out, b.ldo = _m(out)
+        b.eps, b.momentum = float(eps), float(momentum)
+        b.nbt = _p(num_batches_tracked)
+        rc = _gemm_tc_bn(C.byref(g), C.byref(b), _stream())
+        if rc == 0:
+            return out
+        if rc != UNSUPPORTED:
+            raise NativeError(f"ftg_gemm_tc_bn failed with code {rc}")
+    linear(x, w, a_out, bias=bias, precision=precision)
+    bn_relu_fwd(a_out, gamma, beta, running_mean, running_var, out, save_mean, save_invstd, training=True, eps=eps,
+                momentum=momentum, num_batches_tracked=num_batches_tracked)
+    return out
+
+
+def set_fused_bn(on: bool):
+    global _fused_bn
+    _fused_bn = bool(on)
+
+
 def set_gemm_stages(stages: int):
     """Force the tcgen05 GEMM's TMA ring depth (2..6); 0 restores the automatic policy."""
     lib.ftg_gemm_tc_set_stages(int(stages))
+
+
+def set_cluster_push(on: bool):
+    """In-cluster split-K reduction protocol of the tcgen05 GEMM: push (st.async, default) or pull."""
+    lib.ftg_gemm_tc_set_cluster_push(int(bool(on)))
 
 
 def set_gemm_persistent(on: bool):
@@ -531,11 +595,20 @@ def _ptr_array(ptrs):
     return arr
 
 
+def _weights_arg(weights, world):
+    """Host list -> by-value float array; CUDA tensor -> its device pointer (the kernel reads the weights when it
+    runs, e.g. straight from ``fed_stats_to_weights``)."""
+    if torch.is_tensor(weights) and weights.is_cuda:
+        assert weights.dtype == torch.float32 and weights.numel() >= world and weights.is_contiguous()
+        return C.c_void_p(weights.data_ptr())
+    return C.cast((C.c_float * world)(*[float(x) for x in weights]), C.c_void_p)
+
+
 def fedavg_local(arenas, weights, int_offsets=()):
     """All replicas on this GPU: one launch over all ranks' data."""
     n = arenas[0].numel()
     pa = _ptr_array([a.data_ptr() for a in arenas])
-    w = (C.c_float * len(arenas))(*[float(x) for x in weights])
+    w = _weights_arg(weights, len(arenas))
     io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
     _ck(_fedavg_local(pa, len(arenas), w, n, io, len(int_offsets), _stream()), "fedavg_local")
     return arenas
@@ -544,7 +617,7 @@ def fedavg_local(arenas, weights, int_offsets=()):
 def fedavg_twoshot(peer_ptrs, flag_ptrs, rank, weights, n, int_offsets, round_id, status, timeout_ms=20000):
     world = len(peer_ptrs)
     pa, fa = _ptr_array(peer_ptrs), _ptr_array(flag_ptrs)
-    w = (C.c_float * world)(*[float(x) for x in weights])
+    w = _weights_arg(weights, world)
     io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
     _ck(_fedavg_twoshot(pa, fa, rank, world, w, n, io, len(int_offsets), int(round_id), _p(status), int(timeout_ms),
                         _stream()), "fedavg_twoshot")
@@ -553,7 +626,7 @@ def fedavg_twoshot(peer_ptrs, flag_ptrs, rank, weights, n, int_offsets, round_id
 def fedavg_oneshot(peer_ptrs, flag_ptrs, staging, rank, weights, n, int_offsets, round_id, status, timeout_ms=20000):
     world = len(peer_ptrs)
     pa, fa = _ptr_array(peer_ptrs), _ptr_array(flag_ptrs)
-    w = (C.c_float * world)(*[float(x) for x in weights])
+    w = _weights_arg(weights, world)
     io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
     _ck(_fedavg_oneshot(pa, fa, _p(staging), rank, world, w, n, io, len(int_offsets), int(round_id), _p(status),
                         int(timeout_ms), _stream()), "fedavg_oneshot")
@@ -562,7 +635,7 @@ def fedavg_oneshot(peer_ptrs, flag_ptrs, staging, rank, weights, n, int_offsets,
 def fedavg_nvls(peer_ptrs, flag_ptrs, multicast_ptr, rank, weights, n, int_offsets, round_id, status, timeout_ms=20000):
     world = len(peer_ptrs)
     pa, fa = _ptr_array(peer_ptrs), _ptr_array(flag_ptrs)
-    w = (C.c_float * world)(*[float(x) for x in weights])
+    w = _weights_arg(weights, world)
     io = (C.c_int * max(len(int_offsets), 1))(*[int(x) for x in int_offsets])
     _ck(_fedavg_nvls(pa, fa, multicast_ptr, rank, world, w, n, io, len(int_offsets), int(round_id), _p(status),
                      int(timeout_ms), _stream()), "fedavg_nvls")
@@ -608,6 +681,73 @@ def stats_to_weights(hist, cat_off, pool_sorted, client_sorted, smp_off, rows):
                _p(client_sorted) if n_cont else None, _p(smp_off) if n_cont else None, n_cont, _p(rows), _p(jsd),
                _p(wd), _p(w), _stream()), "stats_to_weights")
     return jsd[:, :n_cat], wd[:, :n_cont], w
+
+
+def sort_pad(n: int) -> int:
+    """Row pitch (power of two >= 4096) of the sorted-sample buffers of ``gmm_sample_sort``."""
+    return int(_sort_pad(int(n)))
+
+
+def sort_rows(x):
+    """Every row of ``x`` ([C, n] fp32 CUDA) sorted ascending by the in-kernel bitonic network -> ``[C, sort_pad(n)]``
+    (padding +inf).  No library sort."""
+    assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
+    Cn, n = x.shape
+    out = torch.empty(Cn, sort_pad(n), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _ck(_sort_rows(_p(x), Cn, n, _p(out), _stream()), "sort_rows")
+    return out
+
+
+def quantile_centers(x, K):
+    """``[C, K]`` quantiles (k+0.5)/K of every row of ``x``: the k-means seeds of ``vbgmm_fit``."""
+    n = x.shape[1]
+    srt = sort_rows(x)
+    q = ((torch.arange(K, device=x.device, dtype=torch.float64) + 0.5) / K * (n - 1)).round().long()
+    return srt[:, q].contiguous()
+
+
+def gmm_sample_sort(gmm, n, seed, client_id, out=None):
+    """Draw ``n`` samples from each of the C mixtures ``gmm`` ([C, 7, K] fp64 CUDA, ``vbgmm_fit`` layout) and sort
+    them inside the kernel.  Returns ``[C, sort_pad(n)]`` fp32 (first ``n`` of a row ascending, padding +inf)."""
+    assert gmm.is_cuda and gmm.dtype == torch.float64 and gmm.is_contiguous() and gmm.dim() == 3 and gmm.shape[1] == 7
+    Cn, _, K = gmm.shape
+    pad = sort_pad(n)
+    if out is None:
+        out = torch.empty(Cn, pad, dtype=torch.float32, device=gmm.device)
+    assert out.shape == (Cn, pad) and out.is_contiguous()
+    with torch.cuda.device(gmm.device):
+        _ck(_gmm_sample_sort(_p(gmm), Cn, K, int(n), int(seed) & ((1 << 64) - 1), int(client_id), _p(out), _stream()),
+            "gmm_sample_sort")
+    return out
+
+
+def fed_stats_to_weights(hist_ptrs, seg_ptrs, n_i, rows, cat_off, n_cont, device, K=10, want_pool=False, chunks=None):
+    """Fused federated statistics -> aggregation weights.  ``hist_ptrs`` / ``seg_ptrs``: per-client
+    device pointers (ints; local or peer-mapped) to the category histogram and to the sorted samples of
+    ``gmm_sample_sort``.  Returns ``(jsd [W, n_cat], wd [W, n_cont], weights [W], centers [n_cont, K] | None,
+    pool [n_cont, sum n_i] | None)`` -- all device tensors; ``weights`` can be handed to ``fedavg_*`` as is."""
+    world = len(rows)
+    n_cat = int(cat_off.numel()) - 1 if cat_off is not None else 0
+    dev = torch.device(device)
+    n_total = int(sum(int(x) for x in n_i)) if n_cont else 0
+    if chunks is None:
+        chunks = max(1, min(256, (n_total + 1023) // 1024))
+    f32 = dict(dtype=torch.float32, device=dev)
+    jsd = torch.zeros(world, max(n_cat, 1), **f32)
+    wd = torch.zeros(world, max(n_cont, 1), **f32)
+    w = torch.zeros(world, **f32)
+    partial = torch.zeros(max(n_cont, 1) * chunks * world, **f32)
+    centers = torch.zeros(n_cont, K, **f32) if n_cont else None
+    pool = torch.empty(n_cont, n_total, **f32) if (n_cont and want_pool) else None
+    hp = _ptr_array([int(x) for x in hist_ptrs]) if n_cat else None
+    sp = _ptr_array([int(x) for x in seg_ptrs]) if n_cont else None
+    ni = (C.c_int * world)(*[int(x) for x in (n_i if n_cont else [0] * world)])
+    rw = (C.c_float * world)(*[float(x) for x in rows])
+    with torch.cuda.device(dev):
+        _ck(_fed_stats(hp, sp, ni, rw, world, n_cat, _p(cat_off) if n_cat else None, int(n_cont), _p(partial), chunks,
+                       _p(centers), K, _p(pool), _p(jsd), _p(wd), _p(w), _stream()), "fed_stats_to_weights")
+    return jsd[:, :n_cat], wd[:, :n_cont], w, centers, pool
 
 
 def vbgmm_fit(x, init_centers, dp_prior=1e-3, max_iter=100, tol=1e-3, reg_covar=1e-6, lloyd_iters=16):

@@ -151,6 +151,14 @@ def bn_relu_fwd(a, gamma, beta, running_mean, running_var, out, save_mean, save_
     return out
 
 
+def linear_bn_relu(x, w, a_out, out, *, bias, gamma, beta, running_mean, running_var, save_mean=None, save_invstd=None,
+                   eps=1e-5, momentum=0.1, num_batches_tracked=None, precision=None):
+    """``a_out = x @ w.T + bias``; ``out = relu(batchnorm_train(a_out))`` (Residual block, ``ctgan.py:40-44``)."""
+    linear(x, w, a_out, bias=bias)
+    return bn_relu_fwd(a_out, gamma, beta, running_mean, running_var, out, save_mean, save_invstd, training=True,
+                       eps=eps, momentum=momentum, num_batches_tracked=num_batches_tracked)
+
+
 def bn_relu_bwd(dout, a, save_mean, save_invstd, gamma, beta, da, dgamma, dbeta, dbias_fc=None):
     """Backward of ``relu(bn_train(a))``.  ``dgamma``/``dbeta`` are overwritten; ``dbias_fc``
     (optional) receives the column sum of ``da`` = gradient of the preceding Linear's bias."""

@@ -144,7 +144,27 @@ class MDGANServer:
         self.model_weights_by_number = [r / n_total for r in rows]
         cfg = self.cfg
 
+        cont_ids_all = [ci for ci, col in enumerate(self.meta_transformer) if col["type"] == CONTINUOUS]
+        dev_stats = None
+        if self._device_stats_ok():
+            # K14/K15 on the device: every client's sample is drawn + sorted by a kernel and the fused
+            # statistics kernels read all clients' histograms / samples through device (peer) pointers
+            dev_stats = self.group.device_statistics(models, cont_ids_all, self.category_count_vectors, rows,
+                                                     self.device, seed=self.seed + 7, K=cfg.n_clusters)
+        self.device_stats = dev_stats
+
         def build():
+            if dev_stats is not None:
+                jsd_d, wd_d, w_d = dev_stats.host()
+                if not cont_ids_all:
+                    return wd_d, cont_ids_all, [], (jsd_d, wd_d, w_d)
+                if self.vgm_backend == "vb":
+                    fitted = fit_vbgmm_1d(dev_stats.pool, cfg.n_clusters, cfg.dp_prior, device=self.device,
+                                          init_centers=dev_stats.centers)
+                else:
+                    pool_h = dev_stats.pool.cpu().numpy()
+                    fitted = [fit_sklearn_1d(p, cfg.n_clusters, cfg.dp_prior, random_state=self.seed) for p in pool_h]
+                return wd_d, cont_ids_all, [f.to_array() for f in fitted], (jsd_d, wd_d, w_d)
             samples, pooled, cont_ids = [], [], []
             for ci, col in enumerate(self.meta_transformer):
                 if col["type"] != CONTINUOUS:
@@ -155,14 +175,11 @@ class MDGANServer:
                 samples.append(per_client)
                 pooled.append(np.concatenate(per_client))
             wd = W.continuous_similarity(samples) if samples else np.zeros((self.group.n, 0))
-            dev_w = self._device_similarity(samples)
-            if dev_w is not None:
-                wd = dev_w[1]
             if self.vgm_backend == "vb" and pooled:
                 fitted = fit_vbgmm_1d(np.stack(pooled), cfg.n_clusters, cfg.dp_prior, device=self.device)
             else:
                 fitted = [fit_sklearn_1d(p, cfg.n_clusters, cfg.dp_prior, random_state=self.seed) for p in pooled]
-            return wd, cont_ids, [f.to_array() for f in fitted], dev_w
+            return wd, cont_ids, [f.to_array() for f in fitted], None
 
         wd, cont_ids, fitted, dev_w = self.group.root_compute(build)
         self.distribution_similarity_vector_continuous = wd
@@ -181,35 +198,19 @@ class MDGANServer:
         wire = [None if m is None else m.to_array() for m in agg_models]
         self.group.call("register_transformer_information", wire, agg_comps)
 
-    def _device_similarity(self, samples):
-        """JSD / WD / final weights on the device (``ftg_stats_to_weights``): category
-        histograms and sorted GMM samples go up once, the normalised distance matrices and the
-        soft-maxed weights come back.  ``None`` when there is no GPU (numpy path is used)."""
+    def _device_stats_ok(self):
+        """Device path of the initialisation statistics: needs a CUDA federator device and the native library
+        (``FEDTGAN_DEVICE_STATS=0`` forces the numpy / scipy restatement of the reference)."""
         dev = self.device
-        if dev is None or dev.type != "cuda":
-            return None
+        if dev is None or dev.type != "cuda" or os.environ.get("FEDTGAN_DEVICE_STATS", "1") == "0":
+            return False
+        if self.group.n > 16:
+            return False
         try:
-            from ..ops import native
+            from ..ops import native  # noqa: F401
         except Exception:
-            return None
-        n = self.group.n
-        cv = self.category_count_vectors
-        t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).to(dev)  # noqa: E731
-        with torch.cuda.device(dev):
-            if cv:
-                hist = np.stack([np.concatenate([cv[c][i] for c in range(len(cv))]) for i in range(n)])
-                cat_off = np.concatenate([[0], np.cumsum([len(cv[c][0]) for c in range(len(cv))])])
-            else:
-                hist, cat_off = np.zeros((n, 1)), np.zeros(1)
-            if samples:
-                pool = torch.stack([torch.sort(t(np.concatenate(per), torch.float32)).values for per in samples])
-                flat = torch.cat([torch.sort(t(x, torch.float32)).values for per in samples for x in per])
-                off = np.concatenate([[0], np.cumsum([len(x) for per in samples for x in per])])
-            else:
-                pool, flat, off = None, None, np.zeros(1)
-            jsd, wd, w = native.stats_to_weights(t(hist, torch.float32), t(cat_off, torch.int32), pool, flat,
-                                                 t(off, torch.int32), t(self.rows_number_list, torch.float32))
-            return jsd.double().cpu().numpy(), wd.double().cpu().numpy(), w.double().cpu().numpy()
+            return False
+        return True
 
     def refit_local_transformer(self):
         # the reference walks the clients sequentially (:832-835); they are independent, so
@@ -220,10 +221,13 @@ class MDGANServer:
         host = W.final_weights(self.distribution_similarity_vector, self.distribution_similarity_vector_continuous,
                                self.rows_number_list)
         dev_w = getattr(self, "device_similarity", None)
+        self.weights_device = None
         if dev_w is not None:
-            # the fused kernel's result is the one used; the numpy restatement is the cross-check
+            # the fused kernel's result is the one used (and it stays on the device: the aggregation kernels
+            # read it from there); the numpy restatement is the cross-check
             if np.allclose(dev_w[2], host, atol=2e-3):
                 self.weights_con_cat_combination = dev_w[2] / dev_w[2].sum()
+                self.weights_device = self.device_stats.weights
             else:                                   # never train on weights the two paths disagree about
                 import warnings
 
@@ -232,6 +236,14 @@ class MDGANServer:
         else:
             self.weights_con_cat_combination = host
         return self.weights_con_cat_combination
+
+    def aggregation_weights(self):
+        """What ``group.aggregate`` should be given: the device tensor written by the fused statistics kernel
+        when there is one (the fedavg kernels read it in place), else the host array."""
+        wdev = getattr(self, "weights_device", None)
+        if wdev is not None and getattr(self.group, "accepts_device_weights", False):
+            return wdev
+        return np.asarray(self.weights_con_cat_combination, dtype=np.float64)
 
     # ----------------------------------------------------------- sampling side
     def server_local_synthesizer_initialization(self):
@@ -387,7 +399,7 @@ class MDGANServer:
         self.warm_generation()
         if self.resume:
             self._try_resume()
-        w = np.asarray(self.weights_con_cat_combination, dtype=np.float64)
+        w = self.aggregation_weights()
         for i in range(self.start_epoch, self.epochs):
             t_in = time.time()
             self.group.run("run_local_epochs", 1)

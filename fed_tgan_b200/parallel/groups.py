@@ -67,6 +67,18 @@ class ClientGroup:
     def shutdown(self):
         pass
 
+    # True when ``aggregate`` can take the weights as a CUDA tensor (read by the kernel in place)
+    accepts_device_weights = False
+
+    def device_statistics(self, models, cont_ids, count_vectors, rows, device, seed=0, K=10):
+        """Initialisation statistics on the device.  Default: this process holds every
+        client's mixtures, so it draws + sorts all samples on its own GPU (``devstats.local_statistics``)."""
+        if not self.is_root:
+            return None
+        from .devstats import local_statistics
+
+        return local_statistics(models, cont_ids, count_vectors, rows, device, seed=seed, K=K)
+
 
 def _average_state_dicts(dicts, weights):
     """Reference ``average_model`` (``distributed.py:86-106``): every key, fixed client order,
@@ -83,6 +95,8 @@ def _average_state_dicts(dicts, weights):
 
 
 class LocalGroup(ClientGroup):
+    accepts_device_weights = True
+
     def __init__(self, clients):
         self.clients = list(clients)
         self.n = len(self.clients)
@@ -111,6 +125,8 @@ class LocalGroup(ClientGroup):
                 arenas = [getattr(e, which) for e in engines]
                 native.fedavg_local([a.data for a in arenas], weights, arenas[0].int_slot_offsets())
         else:
+            if torch.is_tensor(weights):
+                weights = weights.detach().cpu().tolist()
             for which in ("G", "D"):
                 arenas = [getattr(e, which) for e in engines]
                 ref_ops.fedavg([a.data for a in arenas], weights, arenas[0].int_slot_offsets())
@@ -180,6 +196,16 @@ class RpcGroup(ClientGroup):
 
 class SpmdGroup(ClientGroup):
     """Every rank owns one client; collective calls all-gather their results."""
+
+    accepts_device_weights = True
+
+    def device_statistics(self, models, cont_ids, count_vectors, rows, device, seed=0, K=10):
+        """Collective: each rank publishes only its own histogram + sorted GMM sample in a CUDA-IPC block and
+        every rank's fused kernels read the peers' statistics in place over NVLink."""
+        from .devstats import spmd_statistics
+
+        return spmd_statistics(self.rank, models[self.rank], cont_ids, count_vectors, rows, device, pg=self.pg,
+                               seed=seed, K=K)
 
     def __init__(self, client, pg=None, use_symmetric=None, rotate_writers=False):
         self.rotate_writers = rotate_writers
@@ -257,10 +283,12 @@ class SpmdGroup(ClientGroup):
         if symmetric:
             if not self._symm_ready:
                 self._setup_symmetric()
-            self.client.symm_aggregate(list(map(float, weights)), int(round_id))
+            self.client.symm_aggregate(weights if torch.is_tensor(weights) else list(map(float, weights)), int(round_id))
             return
         # gloo / CPU: all-gather the flat arenas, reduce in fixed client order (bit-identical
         # in every rank)
+        if torch.is_tensor(weights):
+            weights = weights.detach().cpu().tolist()
         for arena in (e.G, e.D):
             parts = [torch.empty_like(arena.data) for _ in range(self.n)]
             dist.all_gather(parts, arena.data, group=self.pg)

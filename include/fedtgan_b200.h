@@ -39,7 +39,8 @@ typedef struct {
   const int64_t* rng_state; int rng_stream;
   float alpha, slope, drop_p;
   int accumulate;
-  int x3;   /* ftg_gemm_tc only: 1 = fp32x3 (3xTF32 hi/lo split, fp32-equivalent products), 0 = single-pass tf32 */
+  int x3;   /* ftg_gemm_tc only: 0 = single-pass tf32; 1 = fp32x3 (3xTF32 hi/lo split, fp32-equivalent products);
+             * 2 = fp32x3 with hi = the tensor core's own truncation of the fp32 word (only lo is written) */
 } ftg_gemm_args;
 
 /* fp32 CUDA-core GEMM (exact fp32; fallback + oracle for the tensor-core path) */
@@ -56,6 +57,23 @@ int ftg_gemm_simt(const ftg_gemm_args* args, ftg_stream_t stream);
  * Returns 1000 (FTG_ERR_UNSUPPORTED) when the shape/alignment cannot be handled.        */
 int ftg_gemm_tc(const ftg_gemm_args* args, int split_k, float* workspace, int* tile_counters,
                 ftg_stream_t stream);
+/* Residual block forward in ONE launch: D = A.B^T + bias (pre-activation, kept for the backward pass) and
+ * out = relu(batchnorm_train(D)) stored into a column window of a wider buffer (the torch.cat of
+ * S/dtds/synthesizers/ctgan.py:40-44).  Batch statistics are reduced over all rows inside the kernel
+ * (thread-block cluster over the M-tiles, distributed shared memory, Chan's merge); running_mean /
+ * running_var (momentum, unbiased variance), save_mean / save_invstd and num_batches_tracked are
+ * updated like torch.nn.BatchNorm1d.  Needs M <= 512; otherwise returns 1000 and the caller uses
+ * ftg_gemm_tc + ftg_bn_relu_fwd.  SURVEY K2. */
+typedef struct {
+  const float* gamma; const float* beta;
+  float* running_mean; float* running_var;
+  float* save_mean; float* save_invstd;      /* may be NULL */
+  float* out; int ldo;                       /* relu(bn(.)) destination, row pitch in floats */
+  float eps, momentum;
+  float* nbt;                                /* num_batches_tracked (1 float), may be NULL */
+} ftg_bn_args;
+int ftg_gemm_tc_bn(const ftg_gemm_args* args, const ftg_bn_args* bn, ftg_stream_t stream);
+int ftg_gemm_tc_bn_plan(int M, int K);   /* split-K factor the fused kernel will use; 0 = shape not supported */
 /* (No counterpart in the reference.)  ftg_gemm_tc for callers that cannot allocate device
  * memory -- e.g. a plugin inside a host that owns the whole device heap, an out-of-memory
  * fail-safe path, a loop that cannot take cudaMalloc's device synchronisation.  The split-K
@@ -79,6 +97,10 @@ int ftg_gemm_tc_set_stages(int stages);
  * double-buffered TMEM accumulator).  Off by default. */
 int ftg_gemm_tc_set_persistent(int on);
 int ftg_gemm_tc_choose_cluster_split(int M, int N, int K);
+/* In-cluster split-K reduction protocol: 0 (default) = slice owners pull through remote shared-memory loads
+ * between two cluster barriers; 1 = every CTA pushes the other ranks' slices of its partial tile into the owners'
+ * shared memory with st.async + mbarrier complete_tx.  Both sum in rank order (bitwise identical results). */
+int ftg_gemm_tc_set_cluster_push(int on);
 long long ftg_gemm_tc_workspace_bytes(int M, int N, int split_k);
 int ftg_gemm_tc_num_tiles(int M, int N);
 
@@ -204,8 +226,10 @@ int ftg_vbgmm_fit(const float* x, int C, int n, const float* init_centers, int K
  *     page (>= 4*world ints, zero-initialised).  Ranks synchronise inside the kernel with
  *     system-scope flags; `round_id` must increase by one per call.  `status` (device
  *     int) is set non-zero if a peer did not arrive within `timeout_ms`.                   */
-/* `arenas`/`peers`/`flags`/`weights`/`int_offsets` are small HOST arrays (passed to the kernel
- * by value); the pointers stored in them are device / peer-mapped pointers. */
+/* `arenas`/`peers`/`flags`/`int_offsets` are small HOST arrays (passed to the kernel by value); the pointers
+ * stored in them are device / peer-mapped pointers.  `weights` is either a HOST array (copied by value) or a
+ * DEVICE pointer to `world` floats that the kernel reads when it runs -- e.g. `weights_out` of
+ * ftg_fed_stats_to_weights, so the similarity weights never leave the GPU. */
 int ftg_fedavg_local(float* const* arenas, int world, const float* weights, long long n,
                      const int* int_offsets, int n_int, ftg_stream_t stream);
 int ftg_fedavg_twoshot(float* const* peers, int* const* flags, int rank, int world, const float* weights,
@@ -241,6 +265,31 @@ int ftg_stats_to_weights(const float* hist, int world, int n_cat, const int* cat
                          int n_total, const float* client_sorted, const int* smp_off, int n_cont,
                          const float* rows, float* jsd_out, float* wd_out, float* weights_out,
                          ftg_stream_t stream);
+
+/* ---- federated initialisation statistics over peer memory (SURVEY K14 sampler + K15) ----------
+ * ftg_gmm_sample_sort: for each of a client's C continuous columns draw n samples from its mixture
+ *   (gmm: [C][7][K] fp64 as written by ftg_vbgmm_fit; rows 0..2 = means, variances, weights) with Philox
+ *   and sort them inside the kernel (bitonic, one CTA per column).  out: [C][ftg_sort_pad(n)] floats, the
+ *   first n of each row ascending, the padding +inf.  Replaces client_gmm.sample(...)
+ *   (S/dtds/distributed.py:732-734) and the sort inside scipy's wasserstein_distance.
+ * ftg_fed_stats_to_weights: `hist[i]` / `seg[i]` are device pointers -- LOCAL OR PEER-MAPPED -- to client i's
+ *   category histogram (global label order, columns concatenated, cat_off [n_cat+1]) and to its sorted samples
+ *   from ftg_gmm_sample_sort ([n_cont][ftg_sort_pad(n_i[i])]); `n_i`, `rows` and the pointer arrays are small
+ *   HOST arrays (passed by value).  The kernels read every client's statistics in place (over NVLink for peers)
+ *   and write the column-normalised JSD [world][n_cat], WD [world][n_cont] and the soft-maxed weights [world]
+ *   to device memory; ftg_fedavg_* accept that `weights_out` pointer directly.  Optional outputs: `centers`
+ *   [n_cont][K] pooled quantiles ((k+0.5)/K, seeds of the global mixture refit), `pool_out` [n_cont][sum n_i]
+ *   the pooled sample.  `partial`: scratch of n_cont*chunks*world floats.
+ *   Replaces S/dtds/distributed.py:592-686 (JSD part), 689-765 (WD part), 767-783.              */
+int ftg_sort_pad(int n);
+/* rows of x [C][n] sorted ascending into out [C][ftg_sort_pad(n)] (padding +inf), same in-kernel bitonic network */
+int ftg_sort_rows(const float* x, int C, int n, float* out, ftg_stream_t stream);
+int ftg_gmm_sample_sort(const double* gmm, int C, int K, int n, unsigned long long seed, int client_id, float* out,
+                        ftg_stream_t stream);
+int ftg_fed_stats_to_weights(const float* const* hist, const float* const* seg, const int* n_i, const float* rows,
+                             int world, int n_cat, const int* cat_off, int n_cont, float* partial, int chunks,
+                             float* centers, int K, float* pool_out, float* jsd_out, float* wd_out,
+                             float* weights_out, ftg_stream_t stream);
 
 /* ---- host-side CSV writer (S/dtds/distributed.py:586-590 DataFrame.to_csv) --------------- */
 int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,

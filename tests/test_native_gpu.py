@@ -88,6 +88,16 @@ def test_gemm_fp32x3_tcgen05(N, shape):
     assert N.simt_fallback_count() == before, "fp32x3 must run on the tensor cores, not on the SIMT fallback"
 
 
+@pytest.mark.parametrize("shape", GEMM_SHAPES[:6], ids=lambda s: "x".join(map(str, s)))
+def test_gemm_fp32x3_lo_only_variant(N, shape):
+    """Splitter variant 2 (hi = hardware truncation, only lo written) must meet the same fp32 tolerance."""
+    N.set_x3_mode(2)
+    try:
+        _gemm_case(N, *shape, "fp32x3")
+    finally:
+        N.set_x3_mode(1)
+
+
 def test_gemm_fp32x3_beats_tf32_error(N):
     """On one shape: the error of fp32x3 vs an fp64 product is >= 100x smaller than single-pass tf32's."""
     M, Nn, K = 500, 256, 880
@@ -116,6 +126,72 @@ def test_gemm_epilogues(N, prec):
     _gemm_case(N, M, Nn, K, False, True, prec, mask_in=mask)
     _gemm_case(N, M, Nn, K, False, False, prec, accumulate=True, alpha=0.5)
     _gemm_case(N, 50, 256, 5020, False, False, prec, bias=bias, mask_in=mask[:50])
+
+
+@pytest.mark.parametrize("prec", ["fp32x3", "tf32"])
+@pytest.mark.parametrize("shape", [(500, 256, 250), (500, 256, 506), (300, 64, 100), (130, 70, 64), (512, 250, 762),
+                                   (40, 32, 52)], ids=lambda s: "x".join(map(str, s)))
+def test_linear_bn_relu_fused_epilogue(N, shape, prec):
+    """Linear + BatchNorm1d(train) + ReLU + concat-store as ONE tcgen05 launch (cluster over the M-tiles,
+    DSMEM statistics) vs the fp32 torch composition of the same ops (reference Residual, ctgan.py:40-44)."""
+    B, H, K = shape
+    r4 = lambda x: (x + 3) // 4 * 4  # noqa: E731
+    assert N._gemm_tc_bn_plan(B, K) > 0
+    wide = rnd(B, r4(K) + r4(H) + 8, seed=1)                  # [ out window | x ] in one buffer, like `h`
+    w = padded(H, K, r4(K), 2).mul_(0.2)      # in place: keeps the padded leading dimension
+    bias, gamma, beta = rnd(H, seed=3), rnd(H, seed=4).abs() + 0.5, rnd(H, seed=5) * 0.3
+    res = {}
+    for name, fn in (("native", N.linear_bn_relu), ("ref", R.linear_bn_relu)):
+        buf = wide.clone()
+        xx = buf[:, r4(H) + 4: r4(H) + 4 + K]
+        out = buf[:, :H]
+        a = torch.full((B, r4(H)), 7.0, device=dev())[:, :H]
+        rm, rv = rnd(H, seed=6) * 0.1, rnd(H, seed=7).abs() + 0.5
+        sm, si = torch.zeros(H, device=dev()), torch.zeros(H, device=dev())
+        nbt = torch.tensor([3.0], device=dev())
+        n0 = N.launch_count()
+        fn(xx, w, a, out, bias=bias, gamma=gamma, beta=beta, running_mean=rm, running_var=rv, save_mean=sm,
+           save_invstd=si, eps=1e-5, momentum=0.1, num_batches_tracked=nbt, **({"precision": prec} if name == "native" else {}))
+        torch.cuda.synchronize()
+        if name == "native":
+            assert N.launch_count() - n0 == 1, "fused path must be a single launch"
+        res[name] = (a.clone(), out.clone(), rm, rv, sm, si, nbt, buf)
+    tight = prec == "fp32x3"
+    rt, at = (2e-5, 2e-4) if tight else (4e-3, 2e-2)
+    for i, what in enumerate(("pre-activation", "relu(bn)", "running_mean", "running_var", "save_mean", "save_invstd")):
+        got, want = res["native"][i], res["ref"][i]
+        err = (got.double() - want.double()).abs().max().item()
+        assert err <= at + rt * want.abs().max().item(), (what, err)
+    assert res["native"][6].item() == 4.0
+    # nothing outside the output window was touched
+    assert torch.equal(res["native"][7][:, H:], wide[:, H:])
+
+
+@pytest.mark.parametrize("prec", ["tf32", "fp32x3"])
+def test_cluster_splitk_push_equals_pull(N, prec):
+    """The two in-cluster reduction protocols (st.async push / remote-load pull) sum in the same rank order:
+    results are bitwise identical, for every epilogue and for the fused BatchNorm statistics."""
+    shapes = [(500, 256, 506, False, False), (150, 256, 2520, False, False), (50, 2520, 256, False, True),
+              (256, 640, 150, True, True)]
+    for M, Nn, K, a_t, b_t in shapes:
+        r4 = lambda x: (x + 3) // 4 * 4  # noqa: E731
+        a = padded(K, M, r4(M), 1) if a_t else padded(M, K, r4(K), 1)
+        b = padded(K, Nn, r4(Nn), 2) if b_t else padded(Nn, K, r4(K), 2)
+        bias = rnd(Nn, seed=3)
+        outs = []
+        for push in (True, False):
+            N.set_cluster_push(push)
+            try:
+                o = torch.zeros(M, Nn, device=dev())
+                N.linear(a, b, o, a_t=a_t, b_t=b_t, bias=bias, precision=prec)
+                torch.cuda.synchronize()
+                outs.append(o)
+            finally:
+                N.set_cluster_push(False)
+        assert torch.equal(outs[0], outs[1]), (M, Nn, K)
+        ref = torch.zeros(M, Nn, device=dev())
+        R.linear(a, b, ref, a_t=a_t, b_t=b_t, bias=bias)
+        close(outs[0], ref, **(dict(rtol=2e-5, atol=1e-4) if prec == "fp32x3" else dict(rtol=4e-3, atol=4e-3 * (K ** 0.5) / 8)))
 
 
 def test_gemm_splitk_explicit(N):
