@@ -127,7 +127,7 @@ class GMMParams:
 
 
 # --------------------------------------------------------------------------- fit
-def _kmeans_1d(x: torch.Tensor, k: int, iters: int = 16) -> torch.Tensor:
+def _kmeans_1d(x: torch.Tensor, k: int, iters: int = 50) -> torch.Tensor:
     """Batched 1-D Lloyd iterations. x: [C, n] -> hard labels [C, n]."""
     C, n = x.shape
     q = torch.linspace(0.5 / k, 1 - 0.5 / k, k, device=x.device, dtype=x.dtype)

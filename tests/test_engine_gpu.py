@@ -197,3 +197,36 @@ def test_nvls_aggregation_two_gpus():
     if '"unavailable"' in out.stdout or out.returncode != 0:
         pytest.skip("NVLS multicast not usable here: " + (out.stdout + out.stderr)[-300:])   # ... missing NVLS is not
     assert "ALL OK" in out.stdout
+
+
+def _run_two_ranks(script, port, extra_env=None, timeout=240):
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if not k.startswith(("TORCHELASTIC", "RANK", "LOCAL_RANK", "WORLD_SIZE"))}
+    env.update(extra_env or {})
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), os.path.join(root, "tools", script)]
+    return subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
+
+
+@pytest.mark.gpu
+def test_twoshot_aggregation_two_gpus():
+    """Fused P2P two-shot aggregation kernel across two real GPUs vs torch's sum_i w_i theta_i on gathered copies,
+    replicas bitwise identical after write-back (needs 2 GPUs)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = _run_two_ranks("fedavg_mgpu_check.py", 29641, {"FEDAVG_MODES": "twoshot", "FEDAVG_SIZES": "1005472,8000000"})
+    assert out.returncode == 0 and "ALL OK" in out.stdout, (out.stdout + out.stderr)[-2000:]
+
+
+@pytest.mark.gpu
+def test_device_statistics_two_gpus_identical_weights():
+    """SURVEY K15 across processes: each rank publishes its own histogram + sorted GMM sample, every rank's fused
+    kernels read the peers over NVLink; all ranks must end with bit-identical weights equal to the single-process
+    build and to the numpy restatement (needs 2 GPUs)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = _run_two_ranks("spmd_stats_check.py", 29651)
+    assert out.returncode == 0 and "ALL OK" in out.stdout, (out.stdout + out.stderr)[-2000:]

@@ -308,3 +308,43 @@ def test_gemm_host_side_policies():
     assert split(8192, 256, 250) == 1 and split(50, 1024, 31480) == 8
     lib.ftg_gemm_tc_workspace_bytes.restype = C.c_longlong
     assert lib.ftg_gemm_tc_workspace_bytes(150, 256, 4) == 4 * tiles(150, 256) * 128 * 64 * 4
+
+
+def test_vbgmm_active_modes_match_sklearn_on_credit_shape():
+    """The in-house variational DP-GMM decides the encoder shape (``weights_ > 0.005`` active modes, reference
+    ``Server/dtds/features/transformers.py:334-357``).  On the heavy-VGM Credit-shape columns its
+    active-mode count must sit inside sklearn's OWN seed-to-seed spread: BayesianGaussianMixture (k-means++ init,
+    100 unconverged iterations) disagrees with itself across three ``random_state`` values on about half of the
+    columns, by up to 2 modes.  Gate: >= 2/3 of the columns inside sklearn's 3-seed range, never more than 2 modes
+    outside it, mean distance to sklearn's median no larger than sklearn's own mean spread + 0.5, and the mixture's
+    first two moments agree."""
+    import warnings
+
+    from fed_tgan_b200.data.schemas import get_schema, make_table
+    from fed_tgan_b200.features.gmm import fit_sklearn_1d, fit_vbgmm_1d
+
+    schema = get_schema("credit", rows=6000)
+    df = make_table(schema, seed=0)
+    cont = [c for c in schema.columns if c not in schema.categorical]
+    x = np.stack([np.log1p(df[c].to_numpy(np.float64)) if c in schema.nonnegative else df[c].to_numpy(np.float64)
+                  for c in cont])
+    ours = fit_vbgmm_1d(x, 10, 1e-3, device="cpu")
+    outside, dist_med, spread = [], [], []
+    for ci, col in enumerate(x):
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            refs = [fit_sklearn_1d(col, 10, 1e-3, random_state=rs) for rs in (0, 1, 2)]
+        a = int((ours[ci].weights > 0.005).sum())
+        b = [int((r.weights > 0.005).sum()) for r in refs]
+        outside.append(max(min(b) - a, 0) + max(a - max(b), 0))
+        dist_med.append(abs(a - float(np.median(b))))
+        spread.append(max(b) - min(b))
+        ref = refs[0]
+        mo, mr = (ours[ci].weights * ours[ci].means).sum(), (ref.weights * ref.means).sum()
+        vo = (ours[ci].weights * (ours[ci].covs + ours[ci].means ** 2)).sum() - mo ** 2
+        vr = (ref.weights * (ref.covs + ref.means ** 2)).sum() - mr ** 2
+        assert abs(mo - mr) < 0.02 * (1 + abs(mr)) and abs(vo - vr) < 0.05 * (1 + vr), (cont[ci], mo, mr, vo, vr)
+    outside = np.array(outside)
+    assert outside.max() <= 2, outside.tolist()
+    assert (outside == 0).mean() >= 2.0 / 3.0, outside.tolist()
+    assert np.mean(dist_med) <= np.mean(spread) + 0.5, (np.mean(dist_med), np.mean(spread))

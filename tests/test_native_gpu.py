@@ -89,13 +89,14 @@ def test_gemm_fp32x3_tcgen05(N, shape):
 
 
 @pytest.mark.parametrize("shape", GEMM_SHAPES[:6], ids=lambda s: "x".join(map(str, s)))
-def test_gemm_fp32x3_lo_only_variant(N, shape):
-    """Splitter variant 2 (hi = hardware truncation, only lo written) must meet the same fp32 tolerance."""
-    N.set_x3_mode(2)
+def test_gemm_fp32x3_full_split_variant(N, shape):
+    """Splitter variant 1 (hi rewritten as rna_tf32 in place + lo copy) must meet the same fp32 tolerance as the
+    default variant 2 (hi = the tensor core's own truncation, only lo written)."""
+    N.set_x3_mode(1)
     try:
         _gemm_case(N, *shape, "fp32x3")
     finally:
-        N.set_x3_mode(1)
+        N.set_x3_mode(2)
 
 
 def test_gemm_fp32x3_beats_tf32_error(N):
@@ -621,3 +622,99 @@ def test_gemm_persistent_variant_is_bitwise_identical(N):
         assert torch.equal(outs[0], outs[1]), (M, Nn, K)
         ref = (a.t() if a_t else a) @ (b if b_t else b.t()) + bias
         assert ((outs[1] - ref).abs().max() / ref.abs().max()).item() < 5e-3
+
+
+# ------------------------------------------------------------------ federated statistics on the device (K14 / K15)
+def test_sort_rows_in_kernel_bitonic(N):
+    """In-kernel bitonic network (no library sort): ragged sizes, duplicates, more than one shared-memory tile."""
+    for C_, n in ((3, 1000), (2, 4096), (2, 5000), (1, 70001)):
+        g = torch.Generator().manual_seed(n)
+        x = torch.randn(C_, n, generator=g).to(dev())
+        x[:, : n // 7] = x[:, n // 7: 2 * (n // 7)]                    # duplicates
+        out = N.sort_rows(x.contiguous())
+        assert out.shape == (C_, N.sort_pad(n))
+        assert torch.equal(out[:, :n], torch.sort(x, dim=1).values)
+        assert bool(torch.isinf(out[:, n:]).all())
+
+
+def test_gmm_sample_sort_moments_and_order(N):
+    """Device mixture sampler: sorted output, mixture moments and component proportions match
+    (reference: client_gmm.sample(n), Server/dtds/distributed.py:732-734)."""
+    from fed_tgan_b200.features.gmm import GMMParams
+
+    K = 10
+    w = np.array([0.5, 0.3, 0.2] + [0.0] * 7)
+    mu = np.array([0.0, 6.0, -4.0] + [0.0] * 7)
+    var = np.array([1.0, 0.25, 2.0] + [1.0] * 7)
+    g = GMMParams(mu, var, w, np.ones(K), np.ones(K), np.ones(K), np.ones(K))
+    arr = torch.as_tensor(np.stack([g.to_array(), g.to_array()])).to(dev())
+    n = 60000
+    seg = N.gmm_sample_sort(arr, n, seed=11, client_id=3)
+    s = seg[:, :n]
+    assert bool((s[:, 1:] >= s[:, :-1]).all()) and bool(torch.isfinite(s).all())
+    m_true = float((w * mu).sum())
+    v_true = float((w * (var + mu ** 2)).sum() - m_true ** 2)
+    for c in range(2):
+        assert abs(float(s[c].mean()) - m_true) < 0.05
+        assert abs(float(s[c].var()) - v_true) < 0.03 * v_true
+        assert abs(float((s[c] > 3.5).float().mean()) - 0.3) < 0.01       # the mu = 6 component
+    assert not torch.equal(s[0], s[1])                                     # columns draw independent streams
+    again = N.gmm_sample_sort(arr, n, seed=11, client_id=3)
+    assert torch.equal(seg, again)                                         # counter-based: reproducible
+
+
+def test_fed_stats_to_weights_vs_scipy(N):
+    """Fused statistics kernel on the worked-example structure of SURVEY 3.2: JSD vs scipy
+    jensenshannon, WD vs scipy wasserstein_distance ON THE SAME device-drawn samples, weights vs the numpy
+    restatement; pooled quantile seeds and pooled sample are exact."""
+    from scipy.spatial.distance import jensenshannon
+    from scipy.stats import wasserstein_distance
+
+    from fed_tgan_b200.features.gmm import GMMParams
+    from fed_tgan_b200.parallel import weights as W
+    from fed_tgan_b200.parallel.devstats import local_statistics, sample_counts
+
+    K = 10
+    one = np.ones(K)
+
+    def gm(mus, sds, ws):
+        pad = K - len(mus)
+        return GMMParams(np.array(list(mus) + [0.0] * pad), np.array([s * s for s in sds] + [1.0] * pad),
+                         np.array(list(ws) + [0.0] * pad), one, one, one, one)
+
+    rows = [1000, 3000, 2500]
+    models = [[None, gm([0.0], [1.0], [1.0]), gm([1.0, 5.0], [0.5, 1.0], [0.6, 0.4])],
+              [None, gm([2.0], [1.0], [1.0]), gm([1.2, 5.0], [0.5, 1.0], [0.5, 0.5])],
+              [None, gm([1.0], [2.0], [1.0]), gm([0.8, 4.0], [0.6, 1.5], [0.7, 0.3])]]
+    count_vectors = [[np.array([90.0, 10.0]), np.array([10.0, 90.0]), np.array([50.0, 50.0])],
+                     [np.array([5.0, 5.0, 990.0]), np.array([1000.0, 1000.0, 1000.0]), np.array([0.0, 100.0, 2400.0])]]
+    st = local_statistics(models, [1, 2], count_vectors, rows, dev(), seed=5, K=K, want_pool=True)
+    jsd, wd, w = st.host()
+    n_i = sample_counts(rows)
+    # --- JSD
+    for c, col in enumerate(count_vectors):
+        pooled = np.sum(col, axis=0)
+        raw = np.array([jensenshannon(pooled, v) for v in col])
+        assert np.allclose(jsd[:, c], raw / raw.sum(), atol=2e-5), (c, jsd[:, c], raw / raw.sum())
+    # --- WD on the very samples the kernel used (segments are kept alive by the result object)
+    segs = [t for t in st._keep if torch.is_tensor(t) and t.dim() == 2]
+    assert len(segs) == 3
+    for c in range(2):
+        per = [segs[i][c, : n_i[i]].double().cpu().numpy() for i in range(3)]
+        pool = np.concatenate(per)
+        raw = np.array([wasserstein_distance(pool, p) for p in per])
+        assert np.allclose(wd[:, c], raw / raw.sum(), rtol=2e-3, atol=2e-4), (c, wd[:, c], raw / raw.sum())
+        # pooled sample = concatenation in client order; quantile seeds = pooled order statistics
+        assert np.array_equal(st.pool[c].cpu().numpy(), pool.astype(np.float32))
+        srt = np.sort(pool.astype(np.float32))
+        q = np.round((np.arange(K) + 0.5) / K * (len(pool) - 1)).astype(int)
+        assert np.array_equal(st.centers[c].cpu().numpy(), srt[q])
+    # --- final weights vs the numpy restatement of calculate_final_weights_for_aggregation
+    host = W.final_weights(jsd, wd, rows)
+    assert np.allclose(w, host, atol=1e-5) and abs(w.sum() - 1) < 1e-5
+    # --- the aggregation kernel accepts the device weights as they are
+    reps = [torch.randn(4096, device=dev()) for _ in range(3)]
+    want = sum(float(w[i]) * reps[i] for i in range(3))
+    N.fedavg_local(reps, st.weights, [])
+    torch.cuda.synchronize()
+    assert torch.allclose(reps[0], want, atol=1e-5) and torch.equal(reps[0], reps[1])

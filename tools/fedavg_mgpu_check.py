@@ -24,6 +24,8 @@ dev = torch.device("cuda", local)
 dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 
 sizes = [1_005_472, 2_900_000, 8_000_000, 42_000_000]      # floats: Adult G+D, Intrusion, ..., wide 1024 nets
+if os.environ.get("FEDAVG_SIZES"):
+    sizes = [int(x) for x in os.environ["FEDAVG_SIZES"].split(",")]
 n_max = max(sizes)
 ipc_blk = SymmetricBlock(n_max, dev)
 handles = [None] * world

@@ -44,7 +44,13 @@ df = make_table(schema, seed=0, correlated=correlated)
 df_test = make_table(schema, seed=1, rows=10000, correlated=correlated) if correlated > 0 else None
 shards = split_table(df, n_clients, "iid", seed=0)
 dev = "cuda:0" if torch.cuda.is_available() else "cpu"
-out = {"config": config, "epochs": epochs, "clients": n_clients, "rows": len(df), "device": dev,
+precision = None
+if dev != "cpu":
+    from fed_tgan_b200.ops import native  # noqa: E402
+
+    native.set_precision(os.environ.get("PARITY_PRECISION", native.get_precision()))
+    precision = native.get_precision()
+out = {"config": config, "epochs": epochs, "clients": n_clients, "rows": len(df), "device": dev, "precision_ours": precision,
        "correlated_target": correlated, "ours": [], "reference": []}
 
 
@@ -118,6 +124,8 @@ def summary(arm):
     w = np.array([r["avg_wd"] for r in out[arm]])
     return {"final_avg_jsd_mean": float(j[:, -1].mean()), "final_avg_jsd_std": float(j[:, -1].std()),
             "final_avg_wd_mean": float(w[:, -1].mean()), "final_avg_wd_std": float(w[:, -1].std()),
+            "last5_avg_jsd_mean": float(j[:, -5:].mean(1).mean()), "last5_avg_jsd_std": float(j[:, -5:].mean(1).std()),
+            "last5_avg_wd_mean": float(w[:, -5:].mean(1).mean()), "last5_avg_wd_std": float(w[:, -5:].mean(1).std()),
             "epoch0_avg_jsd": float(j[:, 0].mean()), "epoch0_avg_wd": float(w[:, 0].mean()),
             "delta_f1_mean": (float(np.mean([r["utility"]["delta_f1"] for r in out[arm]])) if out[arm][0].get("utility") else None),
             "delta_f1_std": (float(np.std([r["utility"]["delta_f1"] for r in out[arm]])) if out[arm][0].get("utility") else None),
