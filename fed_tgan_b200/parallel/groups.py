@@ -251,6 +251,22 @@ class SpmdGroup(ClientGroup):
             self.client.symm.check()
         dist.barrier(group=self.pg)
 
+    def host_barrier(self):
+        dist.barrier(group=self.pg)
+
+    def gather_block(self, n_floats):
+        """Collective: a second CUDA-IPC block per rank (used as rank 0's gather buffer for the distributed
+        generation of the epoch CSV); returns the connected block (``peer_ptrs[r]`` = rank r's copy)."""
+        from .symm import SymmetricBlock
+
+        blk = SymmetricBlock(n_floats, self.client.device)
+        handles = [None] * self.n
+        dist.all_gather_object(handles, blk.export_handle(), group=self.pg)
+        blk.connect(self.rank, handles)
+        dist.barrier(group=self.pg)
+        self._gather_blocks = getattr(self, "_gather_blocks", []) + [blk]
+        return blk
+
     def prepare(self):
         e = self.client.engine
         symmetric = self.use_symmetric if self.use_symmetric is not None else e.device.type == "cuda"
@@ -283,6 +299,8 @@ class SpmdGroup(ClientGroup):
         if symmetric:
             if not self._symm_ready:
                 self._setup_symmetric()
+            if getattr(self, "pre_aggregate", None) is not None:
+                self.pre_aggregate()
             self.client.symm_aggregate(weights if torch.is_tensor(weights) else list(map(float, weights)), int(round_id))
             return
         # gloo / CPU: all-gather the flat arenas, reduce in fixed client order (bit-identical

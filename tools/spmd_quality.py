@@ -59,11 +59,26 @@ if rank == 0:
         j, w = stat_sim_normalize(df, os.path.join(box[0], f"{schema.name}_result", f"{schema.name}_synthesis_epoch_{i}.csv"),
                                   schema.categorical)
         res["avg_jsd"].append(float(j)); res["avg_wd"].append(float(w))
+    # distributed generation: every rank contributed a contiguous share of the rows -- all shares must be there and
+    # look alike (score each share of the last CSV on its own)
+    import pandas as pd
+
+    last = pd.read_csv(os.path.join(box[0], f"{schema.name}_result", f"{schema.name}_synthesis_epoch_{epochs - 1}.csv"))
+    res["csv_rows"] = int(len(last))
+    per = (len(last) + world - 1) // world
+    res["share_avg_jsd"] = []
+    for r in range(world):
+        part = last.iloc[r * per:(r + 1) * per]
+        pth = os.path.join(box[0], f"share_{r}.csv")
+        part.to_csv(pth, index=False)
+        res["share_avg_jsd"].append(float(stat_sim_normalize(df, pth, schema.categorical)[0]))
+    res["distributed_generation"] = getattr(server, "_dg", None) is not None
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", f"spmd_quality_{world}.json"), "w") as fh:
         json.dump(res, fh, indent=1)
     print(json.dumps(res))
     ok = same and min(res["avg_jsd"]) < 0.06 and all(abs(v) < 1e4 for v in losses.values())
+    ok = ok and res["csv_rows"] == cfg.sample_rows and max(res["share_avg_jsd"]) < 2.0 * min(res["share_avg_jsd"]) + 0.02
     print("QUALITY OK" if ok else "QUALITY FAILED")
 dist.barrier()
 dist.destroy_process_group()
