@@ -83,6 +83,7 @@ class MDGANServer:
         self.start_epoch = 0
         self.round_times = []
         self._rid = 0
+        self._csv_done = {}          # epoch index -> wall-clock time at which its CSV was on disk
         os.makedirs(self.models_dir, exist_ok=True)
         os.makedirs(self.result_dir, exist_ok=True)
 
@@ -274,11 +275,17 @@ class MDGANServer:
         if self.meta_base.get("date_info"):
             df, _, _ = Transform.inverse(table_np, self.meta_base, self.label_encoder)
             df.to_csv(path, index=False)
+            self._csv_done[index] = time.time()
             return path
         names, cols = Transform.decode_arrays(table_np, self.meta_base, self.label_encoder, as_codes=True)
         if any(isinstance(c, np.ndarray) and c.dtype == object for c in cols):
             names, cols = Transform.decode_arrays(table_np, self.meta_base, self.label_encoder)
-        write_table_csv(path, names, cols)
+        # a file that nothing else competes with (the last one of a run, or a slow-round configuration) is
+        # formatted by many threads: it is the serial tail of the run; in steady state several files are in
+        # flight at once and share the cores
+        busy = sum(1 for f in self._pending if not f.done())
+        write_table_csv(path, names, cols, n_threads=(min(16, os.cpu_count() or 1) if busy <= 1 else 4))
+        self._csv_done[index] = time.time()
         return path
 
     # ---- asynchronous generation pipeline (device path) --------------------------------
@@ -536,6 +543,7 @@ class MDGANServer:
         if self.resume:
             self._try_resume()
         w = self.aggregation_weights()
+        t_fit = time.time()
         for i in range(self.start_epoch, self.epochs):
             t_in = time.time()
             self.group.run("run_local_epochs", 1)
@@ -551,6 +559,16 @@ class MDGANServer:
                 self.save_checkpoint(i + 1)
         self.drain()
         self.group.barrier()
+        # timestamp_experiment.csv keeps the reference's meaning (``distributed.py:795-829``: the round's clock stops
+        # after its CSV is written, and similarity_analysis.py cumulative-sums the rows into the time at which
+        # each epoch's output existed).  Rounds overlap here (the CSV of round i is written while round i+1
+        # trains), so row i is the time between CSV i-1 and CSV i being on disk; the host-side enqueue times
+        # stay in metrics.jsonl.
+        done = [self._csv_done.get(i) for i in range(self.start_epoch, self.epochs)]
+        if self.write_csv and self.group.is_root and done and all(d is not None for d in done):
+            stamps = np.maximum.accumulate(np.asarray(done)) - t_fit
+            restored = list(self.round_times[: self.start_epoch])          # rounds of a resumed run's first leg
+            self.round_times = restored + [float(x) for x in np.diff(np.concatenate([[0.0], stamps]))]
         if self.group.is_root:
             with open(os.path.join(self.out_dir, "timestamp_experiment.csv"), "w", newline="") as fh:
                 csv.writer(fh, dialect="excel").writerows(np.asarray(self.round_times).reshape(-1, 1))

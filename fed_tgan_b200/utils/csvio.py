@@ -22,11 +22,11 @@ def _native():
         return None
 
 
-def write_table_csv(path, names, cols):
+def write_table_csv(path, names, cols, n_threads=None):
     lib = _native()
     if lib is not None and lib.available():
         try:
-            lib.write_csv(path, names, cols)
+            lib.write_csv(path, names, cols, n_threads=n_threads)
             return path
         except Exception:
             pass

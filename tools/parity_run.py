@@ -54,10 +54,20 @@ out = {"config": config, "epochs": epochs, "clients": n_clients, "rows": len(df)
        "correlated_target": correlated, "ours": [], "reference": []}
 
 
-def utility_gap(result_dir, name):
+def utility_gap(result_dir, name, arm="ours", seed=0):
     if df_test is None:
         return None
+    import shutil
+
     import pandas as pd
+
+    last = os.path.join(result_dir, f"{name}_synthesis_epoch_{epochs - 1}.csv")
+    save = os.environ.get("PARITY_SAVE_LAST")
+    if save:                       # keep the CSV so that the (CPU-only) utility scoring can run off the GPU box
+        os.makedirs(save, exist_ok=True)
+        shutil.copy(last, os.path.join(save, f"{tag}_{arm}_seed{seed}_epoch{epochs - 1}.csv"))
+    if os.environ.get("PARITY_SKIP_UTILITY") == "1":
+        return None
 
     from fed_tgan_b200.eval.utility import utility_difference
 
@@ -91,7 +101,7 @@ for seed in range(seeds if "ours" in arms else 0):
     out["ours"].append({"seed": seed, "wall_s": round(time.time() - t0, 1), "avg_jsd": [x[0] for x in c],
                         "avg_wd": [x[1] for x in c], "round_s": server.round_times,
                         "weights": [float(w) for w in server.weights_con_cat_combination],
-                        "utility": utility_gap(os.path.join(base, f"{schema.name}_result"), schema.name)})
+                        "utility": utility_gap(os.path.join(base, f"{schema.name}_result"), schema.name, "ours", seed)})
     print("ours seed", seed, "final JSD/WD", c[-1], out["ours"][-1]["utility"] and out["ours"][-1]["utility"]["delta_f1"], flush=True)
 
 for seed in range(seeds if "reference" in arms else 0):
@@ -113,7 +123,7 @@ for seed in range(seeds if "reference" in arms else 0):
     times = [float(x) for x in open(os.path.join(base, "server", "timestamp_experiment.csv")).read().split()]
     out["reference"].append({"seed": seed, "wall_s": round(time.time() - t0, 1), "avg_jsd": [x[0] for x in c],
                              "avg_wd": [x[1] for x in c], "round_s": times,
-                             "utility": utility_gap(os.path.join(base, "server", "Intrusion_result"), "Intrusion")})
+                             "utility": utility_gap(os.path.join(base, "server", "Intrusion_result"), "Intrusion", "reference", seed)})
     print("reference seed", seed, "final JSD/WD", c[-1], out["reference"][-1]["utility"] and out["reference"][-1]["utility"]["delta_f1"], flush=True)
 
 
