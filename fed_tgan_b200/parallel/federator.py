@@ -336,6 +336,8 @@ class MDGANServer:
             snap_done = torch.cuda.Event()
             snap_done.record(self._gen_stream)
             cur.wait_event(snap_done)         # the next round may overwrite the arena only after the snapshot
+            if getattr(self.group, "snapshot_sync", False):
+                snap_done.synchronize()       # the trainer is another process (RPC star): no stream orders it
             if self._gen_graph is None:
                 from ..ops import native
 

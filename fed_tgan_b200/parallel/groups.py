@@ -163,6 +163,34 @@ class RpcGroup(ClientGroup):
         handles = self.call("symm_export")
         self.call("symm_connect", per_client=[(i, handles) for i in range(self.n)])
         self.use_symmetric = True
+        self._map_generator(handles[0])
+
+    def _map_generator(self, handle):
+        """Map client 1's arena block into the federator process (CUDA IPC): after every aggregation it holds the
+        averaged generator, so the per-epoch generation reads it in place instead of pulling a pickled state_dict
+        over RPC, re-uploading it and generating synchronously (the reference's data flow, R8/R9)."""
+        if not str(self.server_device).startswith("cuda"):
+            return
+        try:
+            from ..features.layout import TableLayout
+            from ..models.arena import GeneratorArena
+            from ..ops import native
+            from .symm import _CudaBlob
+
+            dev = torch.device(self.server_device)
+            info = self.call_one(0, "get_layout_info")
+            probe = GeneratorArena(self._cfg, TableLayout(info["output_info"]), "cpu", init=False)
+            with torch.cuda.device(dev):
+                ptr = native.symm_open(handle)
+                view = torch.as_tensor(_CudaBlob(ptr, probe.numel), device=dev)
+            self._arena = GeneratorArena(self._cfg, TableLayout(info["output_info"]), dev, storage=view, init=False)
+            self._mapped_ptr = ptr
+            self.local_generator = True          # federator may snapshot it and generate asynchronously
+            self.snapshot_sync = True            # ... but the clients are other processes: finish the snapshot
+                                                 # before the next round is started over RPC
+        except Exception as exc:                 # same-GPU IPC mapping unavailable: keep the state_dict pull
+            warnings.warn(f"could not map the generator arena into the federator ({exc}); using the RPC pull")
+            self._arena, self.local_generator = None, False
 
     def aggregate(self, weights, round_id):
         if self.n == 1:
@@ -182,6 +210,8 @@ class RpcGroup(ClientGroup):
         from ..features.layout import TableLayout
         from ..models.arena import GeneratorArena
 
+        if self.local_generator and self._arena is not None:
+            return self._arena                   # live view of client 1's (averaged) generator
         sd = getattr(self, "_last_g", None)
         if sd is None or self.use_symmetric:
             sd = self.call_one(0, "get_generator_weights")

@@ -23,6 +23,7 @@ for step in "$@"; do
     timeline) timeout 600 $TR --nproc-per-node $a1 tools/round_timeline.py 20 > $tag.log 2>&1; echo "== timeline N=$a1 rc=$?"; tail -3 $tag.log | cut -c1-600;;
     fedavg)   FEDTGAN_AGGREGATION=${a2:-twoshot} timeout 600 $TR --nproc-per-node $a1 tools/fedavg_mgpu_check.py ${a2} > $tag.log 2>&1; echo "== fedavg N=$a1 ${a2} rc=$?"; tail -12 $tag.log | cut -c1-300;;
     quality)  timeout 900 $TR --nproc-per-node $a1 tools/spmd_quality.py ${a2:-6} > $tag.log 2>&1; echo "== quality N=$a1 rc=$?"; tail -2 $tag.log | cut -c1-900;;
+    rpc)      timeout 1500 python tools/rpc_cli_bench.py ${a1:-2} ${a2:-12} > $tag.log 2>&1; echo "== rpc star clients=${a1:-2} rc=$?"; tail -1 $tag.log | cut -c1-700;;
     persist)  timeout 300 python tools/gemm_persist_check.py > $tag.log 2>&1; echo "== persist rc=$?"; tail -5 $tag.log;;
     sweep)    timeout 300 python tools/gemm_stage_sweep.py > $tag.log 2>&1; echo "== sweep rc=$?"; tail -6 $tag.log;;
     parity)   timeout 3000 python tools/parity_run.py ${a1:-20} adult ${a2:-3} > $tag.log 2>&1; echo "== parity rc=$?"; tail -8 $tag.log | cut -c1-300;;
