@@ -48,30 +48,44 @@ def summarise(rep, name):
 
 
 for rep, name in (("prof_gemm_tc.ncu-rep", "ncu_gemm_tc_summary.md"), ("prof_small.ncu-rep", "ncu_small_kernels_summary.md"),
-                  ("prof_fedavg.ncu-rep", "ncu_fedavg_summary.md")):
+                  ("prof_fedavg.ncu-rep", "ncu_fedavg_summary.md"), ("prof_misc.ncu-rep", "ncu_misc_kernels_summary.md"),
+                  ("prof_gemm_x3.ncu-rep", "ncu_gemm_tc_fp32x3_summary.md")):
     p = os.path.join(GO, rep)
     if os.path.exists(p):
         summarise(p, name)
 
 # per-launch durations of one iteration
-lp = os.path.join(GO, "launches_tf32.csv")
-if os.path.exists(lp):
-    lines = [l for l in open(lp) if not l.startswith("==")]
-    rows = list(csv.DictReader(lines))
-    with open(os.path.join(OUT, "launches_iteration_tf32.md"), "w") as fh:
-        fh.write("# Every launch of 2 training iterations + one 8192-row generation chunk (ncu gpu__time_duration, cold cache, serialised)\n\n| # | kernel | grid | block | us |\n|---|---|---|---|---|\n")
-        tot = 0.0
-        for i, r in enumerate(rows):
-            us = float(r["Metric Value"].replace(",", "")) / 1000.0
-            tot += us
-            nm = re.sub(r"\(.*", "", r["Kernel Name"]).replace("void <unnamed>::", "")
-            fh.write(f"| {i} | {nm} | {r['Grid Size']} | {r['Block Size']} | {us:.1f} |\n")
-        fh.write(f"\nsum = {tot:.1f} us over {len(rows)} launches\n")
+for prec_tag in ("tf32", "fp32x3"):
+  lp = os.path.join(GO, f"launches_{prec_tag}.csv")
+  if os.path.exists(lp):
+      lines = [l for l in open(lp) if not l.startswith("==")]
+      rows = list(csv.DictReader(lines))
+      with open(os.path.join(OUT, f"launches_iteration_{prec_tag}.md"), "w") as fh:
+          fh.write("# Every launch of 2 training iterations + one 8192-row generation chunk (ncu gpu__time_duration, cold cache, serialised)\n\n| # | kernel | grid | block | us |\n|---|---|---|---|---|\n")
+          tot = 0.0
+          for i, r in enumerate(rows):
+              us = float(r["Metric Value"].replace(",", "")) / 1000.0
+              tot += us
+              nm = re.sub(r"\(.*", "", r["Kernel Name"]).replace("void <unnamed>::", "")
+              fh.write(f"| {i} | {nm} | {r['Grid Size']} | {r['Block Size']} | {us:.1f} |\n")
+          fh.write(f"\nsum = {tot:.1f} us over {len(rows)} launches\n")
+
+def compact_sass(text):
+    """cuobjdump listing without the hex encodings (instruction address + mnemonic + operands only): ~6x smaller."""
+    out = []
+    for line in text.splitlines():
+        if re.match(r"^\s*/\* 0x[0-9a-f]+ \*/\s*$", line):
+            continue
+        line = re.sub(r"\s*/\* 0x[0-9a-f]+ \*/\s*$", "", line)
+        m = re.match(r"^\s+(/\*[0-9a-f]+\*/)\s+(.*)$", line)
+        out.append(f"{m.group(1)} {m.group(2).rstrip()}" if m else line.rstrip())
+    return "\n".join(out) + "\n"
+
 
 # SASS evidence
 objs = sorted(glob.glob(os.path.join(ROOT, "fed_tgan_b200", "_native", "obj", "*.cu.o")))
 hist_lines = ["# SASS mnemonic evidence per kernel (cuobjdump -sass, sm_100a)", "",
-              "| object | kernel | instrs | UTCHMMA | UTMALDG | LDTM | UTCBAR | SYNCS | UCGABAR/CGA | LDG/STG | RED/ATOM |", "|---|---|---|---|---|---|---|---|---|---|---|"]
+              "| object | kernel | instrs | UTCHMMA | UTMALDG | LDTM | UTCBAR | SYNCS | UCGABAR/CGA | LDG/STG | RED/ATOM | LDGMC (multimem) | STAS (st.async) |", "|---|---|---|---|---|---|---|---|---|---|---|---|---|"]
 for o in objs:
     sass = subprocess.run(["cuobjdump", "-sass", o], stdout=subprocess.PIPE, text=True).stdout
     cur, stats = None, {}
@@ -80,7 +94,7 @@ for o in objs:
         if m:
             cur = subprocess.run(["c++filt", m.group(1)], stdout=subprocess.PIPE, text=True).stdout.strip()
             cur = re.sub(r"^void ", "", cur.replace("(anonymous namespace)::", "")); cur = re.sub(r"\(.*", "", cur)
-            stats[cur] = dict(n=0, mma=0, tma=0, ldtm=0, utcbar=0, syncs=0, cga=0, ldst=0, atom=0)
+            stats[cur] = dict(n=0, mma=0, tma=0, ldtm=0, utcbar=0, syncs=0, cga=0, ldst=0, atom=0, mc=0, stas=0)
             continue
         m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
         if m and cur:
@@ -95,17 +109,36 @@ for o in objs:
             s["cga"] += op.startswith("UCGABAR") or "CGA" in op
             s["ldst"] += op.startswith("LDG") or op.startswith("STG")
             s["atom"] += op.startswith("RED") or op.startswith("ATOM")
+            s["mc"] += op.startswith("LDGMC")
+            s["stas"] += op.startswith("STAS")
     for k, s in stats.items():
-        hist_lines.append(f"| {os.path.basename(o)} | {k[:70]} | {s['n']} | {s['mma']} | {s['tma']} | {s['ldtm']} | {s['utcbar']} | {s['syncs']} | {s['cga']} | {s['ldst']} | {s['atom']} |")
+        hist_lines.append(f"| {os.path.basename(o)} | {k[:70]} | {s['n']} | {s['mma']} | {s['tma']} | {s['ldtm']} | {s['utcbar']} | {s['syncs']} | {s['cga']} | {s['ldst']} | {s['atom']} | {s['mc']} | {s['stas']} |")
+    base_o = os.path.basename(o).replace(".cu.o", "")
+    if "gemm_tc" not in o:
+        # every kernel of this translation unit, in full
+        open(os.path.join(OUT, "sass", f"{base_o}_all_kernels.sass"), "w").write(compact_sass(sass))
+    else:
+        # the tcgen05 GEMM has ~100 template instantiations: keep the representative ones in full --
+        # fp32x3 + fused BatchNorm epilogue (K-major), and the persistent double-buffered-TMEM kernel (bias epilogue)
+        for tag, pat in (("k_gemm_tc_kmajor_bn_fp32x3", "k_gemm_tcILb0ELb0ELi6ELb1E"), ("k_gemm_tc_persist_kmajor_bias", "k_gemm_tc_persistILb0ELb0ELi2E"),
+                         ("k_gemm_tc_wgrad_mnmajor_plain_fp32x3", "k_gemm_tcILb1ELb1ELi0ELb1E")):
+            keep2, on2 = [], False
+            for line in sass.splitlines():
+                if "Function :" in line:
+                    on2 = pat in line
+                if on2:
+                    keep2.append(line)
+            if keep2:
+                open(os.path.join(OUT, "sass", tag + ".sass"), "w").write(compact_sass("\n".join(keep2)))
     if "gemm_tc" in o:
         # full SASS of the forward (K-major, bias epilogue) variant
         keep, on = [], False
         for line in sass.splitlines():
             if "Function :" in line:
-                on = "ILb0ELb0ELi2E" in line
+                on = "k_gemm_tcILb0ELb0ELi2ELb0E" in line
             if on:
                 keep.append(line)
-        open(os.path.join(OUT, "sass", "k_gemm_tc_kmajor_bias.sass"), "w").write("\n".join(keep) + "\n")
+        open(os.path.join(OUT, "sass", "k_gemm_tc_kmajor_bias.sass"), "w").write(compact_sass("\n".join(keep)))
     if "fedavg" in o:
         keep, on = [], False
         for line in sass.splitlines():
@@ -113,9 +146,12 @@ for o in objs:
                 on = "twoshot" in line
             if on:
                 keep.append(line)
-        open(os.path.join(OUT, "sass", "k_fedavg_twoshot.sass"), "w").write("\n".join(keep) + "\n")
+        pass   # (all fedavg kernels are in fedavg_all_kernels.sass)
 open(os.path.join(OUT, "sass", "mnemonic_histogram.md"), "w").write("\n".join(hist_lines) + "\n")
-for f in ("profile_step_tf32_adult.json", "gemm_timeline.json", "fedavg_mgpu_2.json", "fedavg_mgpu_8.json", "fedavg_mgpu_4.json"):
+for f in ("profile_step_tf32_adult.json", "profile_step_fp32x3_adult.json", "profile_step_fp32x3_wide.json", "profile_step_tf32_wide.json",
+          "gemm_timeline.json", "fedavg_mgpu_2.json", "fedavg_mgpu_8.json", "fedavg_mgpu_4.json", "fedavg_mgpu_2_nvls.json",
+          "fedavg_mgpu_8_nvls.json", "round_timeline_1.json", "round_timeline_2.json", "round_timeline_8.json", "spmd_quality_2.json",
+          "parity_adult_native_fp32x3.json", "parity_adult_native_tf32.json", "parity_adult_ref_cpu20.json"):
     p = os.path.join(GO, f)
     if os.path.exists(p):
         open(os.path.join(OUT, f), "w").write(open(p).read())
