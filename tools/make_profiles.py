@@ -24,8 +24,12 @@ KEYS = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_
 
 
 def ncu_raw(rep):
-    res = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-    rows = list(csv.reader(res.stdout.splitlines()))
+    """`rep` is a .ncu-rep (converted here) or the raw-page CSV already extracted on the GPU box (<name>_raw.csv)."""
+    if rep.endswith(".csv"):
+        text = open(rep).read()
+    else:
+        text = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True).stdout
+    rows = list(csv.reader(text.splitlines()))
     if len(rows) < 3:
         return [], []
     return rows[0], rows[2:]
@@ -51,7 +55,10 @@ for rep, name in (("prof_gemm_tc.ncu-rep", "ncu_gemm_tc_summary.md"), ("prof_sma
                   ("prof_fedavg.ncu-rep", "ncu_fedavg_summary.md"), ("prof_misc.ncu-rep", "ncu_misc_kernels_summary.md"),
                   ("prof_gemm_x3.ncu-rep", "ncu_gemm_tc_fp32x3_summary.md")):
     p = os.path.join(GO, rep)
-    if os.path.exists(p):
+    pc = os.path.join(GO, rep.replace(".ncu-rep", "_raw.csv"))
+    if os.path.exists(pc) and os.path.getsize(pc) > 100:
+        summarise(pc, name)
+    elif os.path.exists(p):
         summarise(p, name)
 
 # per-launch durations of one iteration
