@@ -23,6 +23,9 @@ KEYS = ["gpu__time_duration.sum", "launch__registers_per_thread", "launch__grid_
         "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum"]
 
 
+_units = {}
+
+
 def ncu_raw(rep):
     """`rep` is a .ncu-rep (converted here) or the raw-page CSV already extracted on the GPU box (<name>_raw.csv)."""
     if rep.endswith(".csv"):
@@ -32,6 +35,8 @@ def ncu_raw(rep):
     rows = list(csv.reader(text.splitlines()))
     if len(rows) < 3:
         return [], []
+    global _units
+    _units = dict(zip(rows[0], rows[1]))
     return rows[0], rows[2:]
 
 
@@ -42,11 +47,14 @@ def summarise(rep, name):
     cols = [k for k in KEYS if k in hdr]
     lines = [f"# ncu --set full --clock-control none: {os.path.basename(rep)}", "",
              f"Roofline denominators (MEASURED_PEAKS.json): HBM {peaks.get('hbm_gbs')} GB/s, bf16 {peaks.get('bf16_tflops')} TFLOP/s (of measured).", "",
-             "| kernel | grid | " + " | ".join(c.replace('smsp__average_warps_issue_stalled_', 'stall_').replace('_per_issue_active.ratio', '') for c in cols) + " |",
+             "| kernel | grid | " + " | ".join(c.replace('smsp__average_warps_issue_stalled_', 'stall_').replace('_per_issue_active.ratio', '')
+                                               + (f" [{_units.get(c)}]" if _units.get(c) else "") for c in cols) + " |",
              "|---|---|" + "---|" * len(cols)]
     ki, gi = hdr.index("Kernel Name"), hdr.index("Grid Size")
     for d in data:
-        nm = re.sub(r"\(.*", "", d[ki]).replace("void <unnamed>::", "")
+        nm = re.sub(r"\(.*", "", d[ki]).replace("void <unnamed>::", "").replace("<unnamed>::", "")
+        if "at::" in nm or nm.startswith("elementwise_kernel") or "cub::" in nm:
+            continue                      # torch helper launches of the driver script, not this library's kernels
         lines.append(f"| {nm} | {d[gi]} | " + " | ".join(d[hdr.index(c)][:12] for c in cols) + " |")
     open(os.path.join(OUT, name), "w").write("\n".join(lines) + "\n")
 
