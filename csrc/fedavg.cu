@@ -235,12 +235,19 @@ __device__ __forceinline__ void multimem_st(float* mc, float4 v) {
 
 __global__ void __launch_bounds__(512)
 k_fedavg_nvls(Peers P, float* mc_base, int rank, int world, long long n4, IntSlots slots, int round_id, int* status,
-              unsigned long long timeout_ns) {
+              unsigned long long timeout_ns, int uniform) {
   const unsigned long long deadline = globaltimer_ns() + timeout_ns;
   int* myflags = P.f[rank];
   __shared__ int s_last;
-  // phase 0: theta_rank *= w_rank (whole local replica), then tell the peers
-  {
+  // phase 0: theta_rank *= w_rank (whole local replica), then tell the peers.  With equal weights (IID
+  // shards: w_i = 1/N exactly) the switch sums the raw replicas and the common factor is applied to the
+  // reduced value instead: no extra pass over the arena.
+  if (uniform) {
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      signal_peers(P, rank, world, 0, round_id);
+    }
+  } else {
     float4* mine = reinterpret_cast<float4*>(P.p[rank]);
     const float w = peer_weight(P, rank);
     const long long stride0 = (long long)gridDim.x * blockDim.x;
@@ -276,7 +283,8 @@ k_fedavg_nvls(Peers P, float* mc_base, int rank, int world, long long n4, IntSlo
   const long long chunk = (n4 + world - 1) / world;
   const long long lo = (long long)rank * chunk, hi = min(n4, lo + chunk);
   {
-    constexpr int U = 4;                      // independent switch reductions in flight per thread
+    constexpr int U = 8;                      // independent switch reductions in flight per thread
+    const float post = uniform ? peer_weight(P, rank) : 1.f;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long q0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; q0 < hi; q0 += stride * U) {
       float4 acc[U];
@@ -289,6 +297,7 @@ k_fedavg_nvls(Peers P, float* mc_base, int rank, int world, long long n4, IntSlo
       for (int u = 0; u < U; ++u) {
         const long long q = q0 + u * stride;
         if (q < hi) {
+          acc[u].x *= post; acc[u].y *= post; acc[u].z *= post; acc[u].w *= post;
           if (slots.n) acc[u] = trunc_slots(acc[u], q * 4, slots);
           multimem_st(mc_base + q * 4, acc[u]);
         }
@@ -400,8 +409,11 @@ extern "C" int ftg_fedavg_nvls(float* const* peers, int* const* flags, float* mu
   int blocks = ftg_cdiv(n4, 512 * 4);
   if (blocks > 144) blocks = 144;          // CTAs meet at grid-wide counters: keep them co-resident
   if (blocks < 1) blocks = 1;
+  // equal host-side weights (bitwise): skip the pre-scale pass, scale the reduced sum instead
+  int uniform = P.wdev == nullptr;
+  for (int i = 1; i < world && uniform; ++i) uniform = (P.w[i] == P.w[0]);
   k_fedavg_nvls<<<blocks, 512, 0, (cudaStream_t)stream>>>(P, multicast_base, rank, world, n4, S, round_id, status,
-                                                          (unsigned long long)timeout_ms * 1000000ull);
+                                                          (unsigned long long)timeout_ms * 1000000ull, uniform);
   FTG_LAUNCH_CHECK();
   return 0;
 }

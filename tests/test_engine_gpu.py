@@ -197,6 +197,12 @@ def test_nvls_aggregation_two_gpus():
     if '"unavailable"' in out.stdout or out.returncode != 0:
         pytest.skip("NVLS multicast not usable here: " + (out.stdout + out.stderr)[-300:])   # ... missing NVLS is not
     assert "ALL OK" in out.stdout
+    # equal weights take the pre-scale-free path (the common factor is applied to the switch-reduced value)
+    env["FEDAVG_UNIFORM"] = "1"
+    env["FEDAVG_SIZES"] = "1005472"
+    cmd[cmd.index("29631")] = "29633"
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0 and "ALL OK" in out.stdout, (out.stdout + out.stderr)[-1500:]
 
 
 def _run_two_ranks(script, port, extra_env=None, timeout=240):

@@ -41,6 +41,8 @@ if "nvls" in MODES:
             print(json.dumps({"mode": "nvls", "unavailable": repr(exc)[:300]}), flush=True)
         MODES = [m for m in MODES if m != "nvls"]
 w = torch.softmax(torch.arange(world, dtype=torch.float64) * 0.3, 0).tolist()
+if os.environ.get("FEDAVG_UNIFORM") == "1":        # IID shards: equal weights (NVLS then skips its pre-scale pass)
+    w = [1.0 / world] * world
 round_id = 0
 results = []
 ok_all = True
@@ -92,15 +94,23 @@ for mode in MODES:
             nt.append(s.elapsed_time(e))
         tn = torch.tensor(sorted(nt)[len(nt) // 2], device=dev, dtype=torch.float64)
         dist.all_reduce(tn, op=dist.ReduceOp.MAX)
-        bytes_link = (world - 1) * n4 * 4 if mode == "oneshot" else 2 * (world - 1) / world * n4 * 4
-        row = {"mode": mode, "world": world, "floats": n4, "max_err": err, "replicas_equal": equal, "ok": ok,
-               "ms": float(t), "nccl_ms": float(tn), "nvlink_GBps_per_gpu": bytes_link / (float(t) * 1e-3) / 1e9 if mode == "oneshot" else bytes_link / 2 / (float(t) * 1e-3) / 1e9}
+        # bytes crossing THIS GPU's links per direction: two-shot = my loads of shard r from N-1 peers + the peers'
+        # stores of their shards into me (and the mirror image outbound): 2 (N-1)/N P; one-shot: (N-1) P inbound;
+        # NVLS: the reduced shard + the other ranks' multicasts inbound, my contributions + my multicast outbound: P
+        P_bytes = n4 * 4
+        per_dir = {"oneshot": (world - 1) * P_bytes, "nvls": P_bytes}.get(mode, 2 * (world - 1) / world * P_bytes)
+        gbps = per_dir / (float(t) * 1e-3) / 1e9
+        row = {"mode": mode, "world": world, "floats": n4, "uniform_weights": os.environ.get("FEDAVG_UNIFORM") == "1",
+               "max_err": err, "replicas_equal": equal, "ok": ok, "ms": float(t), "nccl_ms": float(tn),
+               "link_bytes_per_direction": per_dir, "nvlink_GBps_per_direction": gbps,
+               "fraction_of_770GBps_peer_copy": gbps / 770.0}
         results.append(row)
         if rank == 0:
             print(json.dumps(row), flush=True)
 if rank == 0:
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    with open(os.path.join(ROOT, "gpurun_out", f"fedavg_mgpu_{world}{'_nvls' if 'nvls' in MODES else ''}.json"), "w") as fh:
+    tagu = "_uniform" if os.environ.get("FEDAVG_UNIFORM") == "1" else ""
+    with open(os.path.join(ROOT, "gpurun_out", f"fedavg_mgpu_{world}{'_nvls' if 'nvls' in MODES else ''}{tagu}.json"), "w") as fh:
         json.dump(results, fh, indent=1)
     print("ALL OK" if ok_all else "FAILED")
 dist.barrier()

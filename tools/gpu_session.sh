@@ -21,7 +21,7 @@ for step in "$@"; do
               else timeout 1200 $TR --nproc-per-node $n bench.py --impl reference --gpus $n --steps ${a2:-3} --warmup 1 > $tag.log 2> $tag.err; fi
               echo "== reference N=$n rc=$?"; grep '^{' $tag.log | cut -c1-420;;
     timeline) timeout 600 $TR --nproc-per-node $a1 tools/round_timeline.py 20 > $tag.log 2>&1; echo "== timeline N=$a1 rc=$?"; tail -3 $tag.log | cut -c1-600;;
-    fedavg)   FEDTGAN_AGGREGATION=${a2:-twoshot} timeout 600 $TR --nproc-per-node $a1 tools/fedavg_mgpu_check.py ${a2} > $tag.log 2>&1; echo "== fedavg N=$a1 ${a2} rc=$?"; tail -12 $tag.log | cut -c1-300;;
+    fedavg)   FEDAVG_MODES=${a2:-twoshot} timeout 600 $TR --nproc-per-node $a1 tools/fedavg_mgpu_check.py > $tag.log 2>&1; echo "== fedavg N=$a1 ${a2:-twoshot} rc=$?"; grep '^{' $tag.log | cut -c1-420 | tail -12;;
     quality)  timeout 900 $TR --nproc-per-node $a1 tools/spmd_quality.py ${a2:-6} > $tag.log 2>&1; echo "== quality N=$a1 rc=$?"; tail -2 $tag.log | cut -c1-900;;
     rpc)      timeout 1500 python tools/rpc_cli_bench.py ${a1:-2} ${a2:-12} > $tag.log 2>&1; echo "== rpc star clients=${a1:-2} rc=$?"; tail -1 $tag.log | cut -c1-700;;
     persist)  timeout 300 python tools/gemm_persist_check.py > $tag.log 2>&1; echo "== persist rc=$?"; tail -5 $tag.log;;
