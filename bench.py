@@ -186,6 +186,8 @@ def run_ours(args):
         if e2e:
             client.read_losses()
 
+    tails = {}
+
     def timed(n_rounds, e2e, tag):
         launches0 = native.launch_count()
         replay0 = client.graph_replays()
@@ -195,7 +197,12 @@ def run_ours(args):
         start.record()
         for i in range(n_rounds):
             one_round(f"{tag}{i}", e2e)
+        t_drain = time.perf_counter()
+        torch.cuda.current_stream().synchronize()
+        t_gpu_done = time.perf_counter()
         server.drain()                          # CSVs of every round are on disk
+        tails[tag] = {"gpu_catch_up_ms": round((t_gpu_done - t_drain) * 1e3, 3),
+                      "csv_tail_ms": round((time.perf_counter() - t_gpu_done) * 1e3, 3)}
         end.record()
         barrier()
         ms = start.elapsed_time(end)
@@ -267,7 +274,7 @@ def run_ours(args):
             "l2": "flushed between rounds (192 MB memset)" if flush is not None else "not flushed",
             "csv_writer": "rotates over ranks" if (world > 1 and args.rotate) else "rank 0 (async side stream + writer pool)",
             "baseline_ref": "README demo 24.2 s/round (Intrusion, 2 clients, unknown HW)",
-            "init_s": round(t_init, 2), "data_dim": client.layout.data_dim, "n_opt": client.layout.n_opt,
+            "tail_of_timed_region_rank0": tails.get("t"), "init_s": round(t_init, 2), "data_dim": client.layout.data_dim, "n_opt": client.layout.n_opt,
             "aggregation_weights": [round(float(x), 5) for x in weights],
         },
     }

@@ -67,9 +67,13 @@ inline char* put_real(char* o, T v, T int_limit) {
 extern "C" {
 
 // kinds: 0 = float64 column, 1 = float32 column, 2 = int64 column, 3 = int32 codes into
-// str_tables[c] (codes index the table directly; its length is taken from the largest code)
-int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
-                  const void* const* columns, const char* const* const* str_tables, int n_threads) {
+// str_tables[c] (codes index the table directly; its length is taken from the largest code),
+// 4 = float32 column holding category CODES (the generator's numeric table): code = clamp((int)v, 0, n_classes[c]-1).
+// `strides` (elements between consecutive rows of a column; NULL = 1 everywhere) lets kinds 1 and 4 read the
+// columns of a row-major [n_rows, ld] float32 table in place -- no per-column host copies / dtype passes.
+int ftg_csv_write_strided(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
+                          const void* const* columns, const int* strides, const int* n_classes,
+                          const char* const* const* str_tables, int n_threads) {
   if (n_rows < 0 || n_cols <= 0) return -2;
   if (n_threads < 1) n_threads = 1;
   if (n_threads > 64) n_threads = 64;
@@ -86,11 +90,16 @@ int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* n
       case 1: w = 16; break;                                 // "-1.17549435e-38" is 15
       case 2: w = 21; break;
       default: {
-        const int32_t* codes = static_cast<const int32_t*>(columns[c]);
         int32_t mx = -1;
-        for (int r = 0; r < n_rows; ++r) {
-          if (codes[r] < 0) return -3;
-          if (codes[r] > mx) mx = codes[r];
+        if (kinds[c] == 4) {
+          if (!n_classes || n_classes[c] < 1) return -5;
+          mx = n_classes[c] - 1;
+        } else {
+          const int32_t* codes = static_cast<const int32_t*>(columns[c]);
+          for (int r = 0; r < n_rows; ++r) {
+            if (codes[r] < 0) return -3;
+            if (codes[r] > mx) mx = codes[r];
+          }
         }
         tables[c].resize((size_t)(mx + 1));
         for (int32_t k = 0; k <= mx; ++k) {
@@ -127,7 +136,16 @@ int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* n
         if (c) *o++ = ',';
         switch (kinds[c]) {
           case 0: o = put_real<double>(o, static_cast<const double*>(columns[c])[r], 9007199254740992.0); break;
-          case 1: o = put_real<float>(o, static_cast<const float*>(columns[c])[r], 16777216.0f); break;
+          case 1: o = put_real<float>(o, static_cast<const float*>(columns[c])[r * (long long)(strides ? strides[c] : 1)], 16777216.0f); break;
+          case 4: {
+            const float v = static_cast<const float*>(columns[c])[r * (long long)(strides ? strides[c] : 1)];
+            int code = (v >= 0.f) ? (int)v : 0;                       // NaN / negative -> 0 (np.clip semantics)
+            if (code > n_classes[c] - 1) code = n_classes[c] - 1;
+            const StrEntry& e = tables[c][code];
+            std::memcpy(o, e.p, e.len);
+            o += e.len;
+            break;
+          }
           case 2: o = std::to_chars(o, o + 24, static_cast<const int64_t*>(columns[c])[r]).ptr; break;
           default: {
             const StrEntry& e = tables[c][static_cast<const int32_t*>(columns[c])[r]];
@@ -156,6 +174,11 @@ int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* n
   ok = (std::fclose(f) == 0) && ok;
   if (buffer.size() > ((size_t)256 << 20)) std::vector<char>().swap(buffer);   // do not pin huge tables
   return ok ? 0 : -4;
+}
+
+int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
+                  const void* const* columns, const char* const* const* str_tables, int n_threads) {
+  return ftg_csv_write_strided(path, n_rows, n_cols, names, kinds, columns, nullptr, nullptr, str_tables, n_threads);
 }
 
 }  // extern "C"

@@ -22,6 +22,10 @@ def _load():
         _lib.ftg_csv_write.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int),
                                        C.POINTER(C.c_void_p), C.POINTER(C.POINTER(C.c_char_p)), C.c_int]
         _lib.ftg_csv_write.restype = C.c_int
+        _lib.ftg_csv_write_strided.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_int),
+                                               C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                               C.POINTER(C.POINTER(C.c_char_p)), C.c_int]
+        _lib.ftg_csv_write_strided.restype = C.c_int
     return _lib
 
 
@@ -70,3 +74,38 @@ def write_csv(path, names, cols, n_threads=None):
     if rc != 0:
         raise OSError(f"ftg_csv_write({path}) failed: {rc}")
     return path
+
+
+class TablePlan:
+    """Everything about a table's CSV that does not change from epoch to epoch (names, kinds, class strings), so
+    that writing one epoch is a single native call over the generator's row-major float32 table."""
+
+    def __init__(self, names, specs):
+        """``specs[j]``: ``("real",)`` float column, or ``("cat", classes)`` float-coded category column."""
+        self.n_cols = len(names)
+        self.c_names = (C.c_char_p * self.n_cols)(*[str(n).encode() for n in names])
+        self.kinds = (C.c_int * self.n_cols)()
+        self.n_classes = (C.c_int * self.n_cols)()
+        self.tables = (C.POINTER(C.c_char_p) * self.n_cols)()
+        self._keep = []
+        for j, sp in enumerate(specs):
+            if sp[0] == "cat":
+                tab = (C.c_char_p * len(sp[1]))(*[str(x).encode() for x in sp[1]])
+                self._keep.append(tab)
+                self.kinds[j], self.n_classes[j] = 4, len(sp[1])
+                self.tables[j] = C.cast(tab, C.POINTER(C.c_char_p))
+            else:
+                self.kinds[j], self.n_classes[j] = 1, 0
+
+    def write(self, path, table: np.ndarray, n_threads=4):
+        assert table.dtype == np.float32 and table.ndim == 2 and table.shape[1] == self.n_cols
+        assert table.strides[1] == 4, "row-major float32 table expected"
+        lib = _load()
+        ld = table.strides[0] // 4
+        ptrs = (C.c_void_p * self.n_cols)(*[table.ctypes.data + 4 * j for j in range(self.n_cols)])
+        strides = (C.c_int * self.n_cols)(*([ld] * self.n_cols))
+        rc = lib.ftg_csv_write_strided(str(path).encode(), table.shape[0], self.n_cols, self.c_names, self.kinds, ptrs,
+                                       strides, self.n_classes, self.tables, int(n_threads))
+        if rc != 0:
+            raise OSError(f"ftg_csv_write_strided({path}) failed: {rc}")
+        return path

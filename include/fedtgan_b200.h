@@ -294,6 +294,11 @@ int ftg_fed_stats_to_weights(const float* const* hist, const float* const* seg, 
 /* ---- host-side CSV writer (S/dtds/distributed.py:586-590 DataFrame.to_csv) --------------- */
 int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
                   const void* const* columns, const char* const* const* str_tables, int n_threads);
+/* same, reading float32 columns (kind 1) and float32-coded categories (kind 4, clamped to n_classes[c]) in place from
+ * a row-major table through per-column strides: the generator's numeric table goes to text without host-side passes */
+int ftg_csv_write_strided(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
+                          const void* const* columns, const int* strides, const int* n_classes,
+                          const char* const* const* str_tables, int n_threads);
 
 const char* ftg_version(void);
 long long ftg_last_launch_count(void);   /* kernels launched by this library since load */

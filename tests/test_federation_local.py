@@ -86,3 +86,32 @@ def test_rebinding_arena_storage_keeps_training_state(tmp_path):
         assert torch.equal(want["opt" + net]["exp_avg"], got["opt" + net]["exp_avg"])
         assert want["opt" + net]["step"] == got["opt" + net]["step"]
     assert torch.equal(want["rng"], got["rng"]) and want["iterations"] == got["iterations"]
+
+
+def test_csv_fast_path_matches_general_decode(tmp_path):
+    """The native strided writer (numeric table -> text in one call) must produce byte-identical files to the
+    general path (per-column decode + column writer), including out-of-range / negative category codes."""
+    import torch
+
+    from fed_tgan_b200.data.transform import Transform
+    from fed_tgan_b200.utils.csvio import write_table_csv
+
+    schema = get_schema("adult", rows=500)
+    df = make_table(schema, seed=4)
+    cfg = CTGANConfig(batch_size=50, gen_dim=(16,), dis_dim=(16,), embedding_dim=8, sample_rows=700, pack=5)
+    c = _clients(schema, [df], cfg)[0]
+    server = MDGANServer([c], epochs=1, config=cfg, name="Adult", out_dir=str(tmp_path), async_csv=False)
+    server.uniform_meta_category(); server.uniform_continuous_gmm(); server.refit_local_transformer()
+    server.calculate_final_weights_for_aggregation(); server.server_local_synthesizer_initialization()
+    table = server.sample(cfg.sample_rows).to(torch.float32).cpu().numpy()
+    cat_cols = [j for j, n in enumerate(schema.columns) if n in schema.categorical]
+    table[3, cat_cols[0]] = 1e6           # beyond the last class -> clamped
+    table[5, cat_cols[1]] = -4.0          # negative -> class 0
+    plan = server._csv_plan()
+    assert plan is not None
+    fast = plan.write(str(tmp_path / "fast.csv"), table, n_threads=3)
+    names, cols = Transform.decode_arrays(table, server.meta_base, server.label_encoder, as_codes=True)
+    slow = write_table_csv(str(tmp_path / "slow.csv"), names, cols, n_threads=2)
+    assert open(fast, "rb").read() == open(slow, "rb").read()
+    back = pd.read_csv(fast)
+    assert list(back.columns) == schema.columns and len(back) == cfg.sample_rows
