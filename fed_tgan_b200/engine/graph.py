@@ -25,8 +25,20 @@ class GraphedIteration:
         self.stream.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(self.stream):
             native.preallocate_scratch(dev)
+            # The warm-up iterations (module load, scratch sizing) must not count as training: the reference's
+            # first local epoch is exactly rows // batch steps (`distributed.py:334`).  Snapshot everything an
+            # iteration changes -- weights + BN buffers, Adam moments, the Philox (seed, step) state -- and put it
+            # back after the warm-up.
+            saved = [t.clone() for t in (engine.G.data, engine.D.data, engine.G.exp_avg, engine.G.exp_avg_sq,
+                                         engine.D.exp_avg, engine.D.exp_avg_sq, engine.rng.state)]
+            it0 = engine.iterations
             for _ in range(warmup):            # un-captured warm-up: loads modules, sizes scratch
                 engine.iteration()
+            self.stream.synchronize()
+            for t, sv in zip((engine.G.data, engine.D.data, engine.G.exp_avg, engine.G.exp_avg_sq,
+                              engine.D.exp_avg, engine.D.exp_avg_sq, engine.rng.state), saved):
+                t.copy_(sv)
+            engine.iterations = it0
             self.stream.synchronize()
             g = torch.cuda.CUDAGraph()
             n0 = native.launch_count()
@@ -35,7 +47,7 @@ class GraphedIteration:
             self.launches_per_replay = native.launch_count() - n0
             self.graph = g
         torch.cuda.current_stream(dev).wait_stream(self.stream)
-        self.warmup_iterations = warmup + 1
+        self.warmup_iterations = 0             # (restored: the warm-up leaves no trace in the training state)
         self.replays = 0
 
     def run(self, steps: int):

@@ -11,7 +11,12 @@ from __future__ import annotations
 
 import torch
 
+import os
+
 FLAG_INTS = 256
+# how long a rank spins at the in-kernel barrier before it gives up and sets the status word.  Shards of very different
+# size (non-IID splits) legitimately arrive far apart; FEDTGAN_BARRIER_TIMEOUT_MS overrides.
+BARRIER_TIMEOUT_MS = int(os.environ.get("FEDTGAN_BARRIER_TIMEOUT_MS", "60000"))
 
 
 class _CudaBlob:
@@ -93,7 +98,8 @@ class SymmetricBlock(_StatusWord):
         self.peer_ptrs = ptrs
         self.peer_flag_ptrs = [p + self.n_floats * 4 for p in ptrs]
 
-    def fedavg(self, weights, n, int_offsets, round_id, mode="twoshot", timeout_ms=20000):
+    def fedavg(self, weights, n, int_offsets, round_id, mode="twoshot", timeout_ms=None):
+        timeout_ms = BARRIER_TIMEOUT_MS if timeout_ms is None else timeout_ms
         n = (int(n) + 3) // 4 * 4
         assert n <= self.n_floats
         with torch.cuda.device(self.device):
@@ -146,7 +152,8 @@ class NvlsBlock(_StatusWord):
         self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
         dist.barrier(group=group)
 
-    def fedavg(self, weights, n, int_offsets, round_id, mode="nvls", timeout_ms=20000):
+    def fedavg(self, weights, n, int_offsets, round_id, mode="nvls", timeout_ms=None):
+        timeout_ms = BARRIER_TIMEOUT_MS if timeout_ms is None else timeout_ms
         n = (int(n) + 3) // 4 * 4
         with torch.cuda.device(self.device):
             if mode == "nvls":

@@ -64,7 +64,12 @@ def test_graph_replay_trains():
 
     cfg, lay, table, eng = small_setup(device="cuda:0", batch=500, pack=10, rows=3000, gen_dim=(256, 256),
                                        dis_dim=(256, 256), emb=128)
+    fresh_g, fresh_d = eng.G.data.clone(), eng.D.data.clone()
     g = GraphedIteration(eng)
+    # warm-up + capture leave no trace: the first local epoch is exactly rows // batch steps (reference :334)
+    assert torch.equal(fresh_g, eng.G.data) and torch.equal(fresh_d, eng.D.data)
+    assert int(eng.rng.state[1].item()) == 0 and eng.iterations == 0
+    assert float(eng.G.exp_avg.abs().max()) == 0.0 and float(eng.D.exp_avg_sq.abs().max()) == 0.0
     before = eng.G.data.clone()
     it0 = int(eng.rng.state[1].item())
     g.run(5)
