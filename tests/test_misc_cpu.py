@@ -111,6 +111,40 @@ def test_cli_flags():
     assert d.port == 7788 and d.world_size == 2 and d.target_column == "class" and len(d.selected_variables) == 42
 
 
+def test_cli_per_client_data(tmp_path):
+    """One-box launches must not train every client on the same rows (reference: one data folder per client):
+    ``{rank}`` / ``{client}`` in -datapath, or ``--split`` shards of one file; default precision is fp32-equivalent."""
+    import warnings
+
+    from fed_tgan_b200.parallel.launcher import _warn_shared_datapath, client_kwargs, config_from_args, resolve_datapath
+
+    assert resolve_datapath("data/Client{rank}/t.csv", 0) == "data/Client1/t.csv"
+    assert resolve_datapath("shard_{client}.csv", 2) == "shard_2.csv"
+    schema = get_schema("adult", rows=300)
+    df = make_table(schema, seed=0)
+    path = tmp_path / "Adult_train.csv"
+    df.to_csv(path, index=False)
+    a = build_parser().parse_args(["-datapath", str(path), "--split", "iid", "-selected_variables", ",".join(schema.columns),
+                                   "-categorical_list", ",".join(schema.categorical), "-nonnegative_list", ",",
+                                   "-target_column", schema.target])
+    assert a.precision == "fp32x3" and config_from_args(a).precision == "fp32x3"
+    cfg = config_from_args(a)
+    seen = []
+    for cid in range(3):
+        kw = client_kwargs(a, cfg, cid, "cpu", 3)
+        assert kw["split"] == ("iid", 3, cid, 0)
+        c = MDGANClient(**kw)
+        seen.append(c._dataframe)
+    assert sum(len(x) for x in seen) == len(df)
+    keys = [set(map(tuple, x.round(6).astype(str).to_numpy())) for x in seen]
+    assert not (keys[0] & keys[1]) and not (keys[1] & keys[2])          # disjoint shards
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        a.split = "none"
+        _warn_shared_datapath(a, 3)
+        assert any("same file" in str(x.message) for x in w)
+
+
 def test_standalone_synthesizer():
     schema = get_schema("adult", rows=400)
     df = make_table(schema, seed=0)
