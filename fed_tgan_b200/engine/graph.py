@@ -45,6 +45,7 @@ class GraphedIteration:
             with torch.cuda.graph(g, stream=self.stream):
                 engine.iteration()
             self.launches_per_replay = native.launch_count() - n0
+            engine.iterations = it0            # the capture pass executed nothing
             self.graph = g
         torch.cuda.current_stream(dev).wait_stream(self.stream)
         self.warmup_iterations = 0             # (restored: the warm-up leaves no trace in the training state)
