@@ -202,7 +202,8 @@ def run_ours(args):
         t_gpu_done = time.perf_counter()
         server.drain()                          # CSVs of every round are on disk
         tails[tag] = {"gpu_catch_up_ms": round((t_gpu_done - t_drain) * 1e3, 3),
-                      "csv_tail_ms": round((time.perf_counter() - t_gpu_done) * 1e3, 3)}
+                      "csv_tail_ms": round((time.perf_counter() - t_gpu_done) * 1e3, 3),
+                      "breakdown": getattr(server, "tail_breakdown_ms", None)}
         end.record()
         barrier()
         ms = start.elapsed_time(end)

@@ -71,9 +71,13 @@ extern "C" {
 // 4 = float32 column holding category CODES (the generator's numeric table): code = clamp((int)v, 0, n_classes[c]-1).
 // `strides` (elements between consecutive rows of a column; NULL = 1 everywhere) lets kinds 1 and 4 read the
 // columns of a row-major [n_rows, ld] float32 table in place -- no per-column host copies / dtype passes.
+// A negative `n_threads` means |n_threads| threads and NO header line (the file is one part of a table whose parts
+// are concatenated by the caller).
 int ftg_csv_write_strided(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
                           const void* const* columns, const int* strides, const int* n_classes,
                           const char* const* const* str_tables, int n_threads) {
+  const bool with_header = n_threads >= 0;
+  if (n_threads < 0) n_threads = -n_threads;
   if (n_rows < 0 || n_cols <= 0) return -2;
   if (n_threads < 1) n_threads = 1;
   if (n_threads > 64) n_threads = 64;
@@ -139,8 +143,9 @@ int ftg_csv_write_strided(const char* path, int n_rows, int n_cols, const char* 
           case 1: o = put_real<float>(o, static_cast<const float*>(columns[c])[r * (long long)(strides ? strides[c] : 1)], 16777216.0f); break;
           case 4: {
             const float v = static_cast<const float*>(columns[c])[r * (long long)(strides ? strides[c] : 1)];
-            int code = (v >= 0.f) ? (int)v : 0;                       // NaN / negative -> 0 (np.clip semantics)
-            if (code > n_classes[c] - 1) code = n_classes[c] - 1;
+            // clamp in float space first: (int) of a huge / infinite float is undefined.  NaN / negative -> 0
+            const float top = (float)(n_classes[c] - 1);
+            const int code = (v >= top) ? n_classes[c] - 1 : (v > 0.f ? (int)v : 0);
             const StrEntry& e = tables[c][code];
             std::memcpy(o, e.p, e.len);
             o += e.len;
@@ -169,7 +174,7 @@ int ftg_csv_write_strided(const char* path, int n_rows, int n_cols, const char* 
   std::string header;
   for (int c = 0; c < n_cols; ++c) { if (c) header.push_back(','); quote_into(header, names[c]); }
   header.push_back('\n');
-  bool ok = std::fwrite(header.data(), 1, header.size(), f) == header.size();
+  bool ok = !with_header || std::fwrite(header.data(), 1, header.size(), f) == header.size();
   for (int t = 0; t < n_threads && ok; ++t) ok = std::fwrite(base + slice * t, 1, used[t], f) == used[t];
   ok = (std::fclose(f) == 0) && ok;
   if (buffer.size() > ((size_t)256 << 20)) std::vector<char>().swap(buffer);   // do not pin huge tables

@@ -97,7 +97,7 @@ class TablePlan:
             else:
                 self.kinds[j], self.n_classes[j] = 1, 0
 
-    def write(self, path, table: np.ndarray, n_threads=4):
+    def write(self, path, table: np.ndarray, n_threads=4, header=True):
         assert table.dtype == np.float32 and table.ndim == 2 and table.shape[1] == self.n_cols
         assert table.strides[1] == 4, "row-major float32 table expected"
         lib = _load()
@@ -105,7 +105,7 @@ class TablePlan:
         ptrs = (C.c_void_p * self.n_cols)(*[table.ctypes.data + 4 * j for j in range(self.n_cols)])
         strides = (C.c_int * self.n_cols)(*([ld] * self.n_cols))
         rc = lib.ftg_csv_write_strided(str(path).encode(), table.shape[0], self.n_cols, self.c_names, self.kinds, ptrs,
-                                       strides, self.n_classes, self.tables, int(n_threads))
+                                       strides, self.n_classes, self.tables, int(n_threads) if header else -int(n_threads))
         if rc != 0:
             raise OSError(f"ftg_csv_write_strided({path}) failed: {rc}")
         return path

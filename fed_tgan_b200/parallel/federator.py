@@ -473,7 +473,8 @@ class MDGANServer:
         self._dg = {"per": per, "ncol": ncol, "block": block, "dst": dst, "pending": None, "d2h_done": None,
                     "out": torch.empty(per, ncol, dtype=torch.float32, device=dev), "round": 0, "graph": None,
                     "gen": RowGenerator(self.cfg, self.layout, self.decode_tables, self.cum_emp, dev,
-                                        seed=self.seed + 4242 + 7919 * g.rank)}
+                                        seed=self.seed + 4242 + 7919 * g.rank),
+                    "tail_host": torch.zeros(per, ncol, dtype=torch.float32).pin_memory()}
         if g.is_root:
             self._dg["tables"] = [block.tensor[s_ * slot_floats:(s_ + 1) * slot_floats].view(N * per, ncol)[:n]
                                   for s_ in range(2)]
@@ -483,6 +484,16 @@ class MDGANServer:
         self._gen_stream = torch.cuda.Stream(device=dev)
         self._snap = GeneratorArena(self.cfg, self.layout, dev, init=False)
         g.pre_aggregate = self._dist_pre_aggregate
+        plan = self._csv_plan() if self.write_csv else None
+        if plan is not None:
+            # the native writer keeps a per-thread formatting buffer: fault it in now on this (the launching) thread,
+            # which formats this rank's share of the LAST table of a run (_dist_flush)
+            warm = os.path.join(self.result_dir, f".warm_{g.rank}.csv")
+            plan.write(warm, self._dg["tail_host"].numpy(), n_threads=self._tail_threads(), header=False)
+            os.remove(warm)
+
+    def _tail_threads(self):
+        return max(1, min(8, (os.cpu_count() or 8) // max(self.group.n, 1)))
 
     def _dist_pre_aggregate(self):
         """Called by the group right before it launches the aggregation kernel: order this rank's share of the
@@ -565,10 +576,46 @@ class MDGANServer:
         if dg["pending"] is None:
             return
         dev = self._snap.device
-        dg["pending"][2].synchronize()
+        slot, index, ev = dg["pending"]
+        ev.synchronize()
         torch.cuda.synchronize(dev)
-        self.group.host_barrier()
-        self._dist_collect(torch.cuda.current_stream(dev))
+        plan = self._csv_plan() if (self.write_csv and index is not None) else None
+        if plan is None or os.environ.get("FEDTGAN_PARALLEL_TAIL", "1") == "0":
+            self.group.host_barrier()
+            self._dist_collect(torch.cuda.current_stream(dev))
+            return
+        # The last table of a run is the serial tail of the whole job: instead of rank 0 formatting all rows, every
+        # rank turns ITS share (still in its own generation buffer) into text and rank 0 concatenates the parts.
+        g, n, per = self.group, self.cfg.sample_rows, dg["per"]
+        rows = max(0, min(n, (g.rank + 1) * per) - g.rank * per)
+        tm = [time.perf_counter()]
+        dg["tail_host"].copy_(dg["out"])
+        tm.append(time.perf_counter())
+        final = os.path.join(self.result_dir, f"{self.name}_synthesis_epoch_{index}.csv")
+        nt = self._tail_threads()
+        if rows > 0:
+            plan.write(f"{final}.part{g.rank}", dg["tail_host"].numpy()[:rows], n_threads=nt, header=g.is_root)
+        tm.append(time.perf_counter())
+        g.host_barrier()
+        tm.append(time.perf_counter())
+        dg["pending"] = None
+        if g.is_root:
+            # part 0 (with the header) becomes the file; the other parts are appended inside the kernel (sendfile)
+            os.replace(f"{final}.part0", final)
+            with open(final, "ab") as out:
+                for r in range(1, g.n):
+                    part = f"{final}.part{r}"
+                    if os.path.exists(part):
+                        with open(part, "rb") as fh:
+                            size, off = os.fstat(fh.fileno()).st_size, 0
+                            while off < size:
+                                off += os.sendfile(out.fileno(), fh.fileno(), off, size - off)
+                        os.remove(part)
+            self._csv_done[index] = time.time()
+            self.d2h_bytes_last = n * dg["ncol"] * 4
+        tm.append(time.perf_counter())
+        self.tail_breakdown_ms = dict(zip(("d2h_share", "format_share", "host_barrier", "concatenate"),
+                                          [round((b - a) * 1e3, 3) for a, b in zip(tm, tm[1:])]))
 
     # ------------------------------------------------------------------ rounds
     def fit(self):

@@ -295,7 +295,8 @@ int ftg_fed_stats_to_weights(const float* const* hist, const float* const* seg, 
 int ftg_csv_write(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
                   const void* const* columns, const char* const* const* str_tables, int n_threads);
 /* same, reading float32 columns (kind 1) and float32-coded categories (kind 4, clamped to n_classes[c]) in place from
- * a row-major table through per-column strides: the generator's numeric table goes to text without host-side passes */
+ * a row-major table through per-column strides: the generator's numeric table goes to text without host-side passes.
+ * n_threads < 0: |n_threads| threads and no header line (one part of a table the caller concatenates). */
 int ftg_csv_write_strided(const char* path, int n_rows, int n_cols, const char* const* names, const int* kinds,
                           const void* const* columns, const int* strides, const int* n_classes,
                           const char* const* const* str_tables, int n_threads);

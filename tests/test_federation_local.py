@@ -115,3 +115,15 @@ def test_csv_fast_path_matches_general_decode(tmp_path):
     assert open(fast, "rb").read() == open(slow, "rb").read()
     back = pd.read_csv(fast)
     assert list(back.columns) == schema.columns and len(back) == cfg.sample_rows
+    # values no integer can hold (numpy's astype is undefined there): the native writer clamps in float space --
+    # huge / +inf -> last class, NaN / -inf -> class 0 -- and never indexes outside the class table
+    wild = table.copy()
+    j = cat_cols[2]
+    wild[6, j], wild[7, j], wild[8, j], wild[9, j] = 3.0e38, float("inf"), float("nan"), float("-inf")
+    got = pd.read_csv(plan.write(str(tmp_path / "wild.csv"), wild, n_threads=2), keep_default_na=False)
+    classes = [str(c) for c in server.label_encoder[2]["label_encoder"].classes_]
+    assert list(got.iloc[6:10, j]) == [classes[-1], classes[-1], classes[0], classes[0]]
+    # header-less part files concatenate to the same bytes
+    a = plan.write(str(tmp_path / "p0.csv"), table[:300], n_threads=2, header=True)
+    b = plan.write(str(tmp_path / "p1.csv"), table[300:], n_threads=3, header=False)
+    assert open(a, "rb").read() + open(b, "rb").read() == open(fast, "rb").read()
