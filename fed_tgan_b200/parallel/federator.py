@@ -602,7 +602,8 @@ class MDGANServer:
         if g.is_root:
             # part 0 (with the header) becomes the file; the other parts are appended inside the kernel (sendfile)
             os.replace(f"{final}.part0", final)
-            with open(final, "ab") as out:
+            with open(final, "r+b") as out:          # (not "ab": sendfile refuses O_APPEND descriptors)
+                out.seek(0, os.SEEK_END)
                 for r in range(1, g.n):
                     part = f"{final}.part{r}"
                     if os.path.exists(part):
