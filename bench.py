@@ -16,6 +16,12 @@ timed with CUDA events; the reported time is the max over ranks.
 ``value`` is measured with the training shard resident on the device; ``e2e`` repeats the
 run through the same public API (``MDGANServer.fit``) but additionally re-stages the
 client's shard host(pinned)->device every round and reads the round's losses back.
+
+The headline runs at ``--precision fp32x3`` (tcgen05 with the 3xTF32 split: fp32-equivalent, like the
+reference's fp32 matmuls); the same line carries ``alt_precision`` (single-pass tf32), ``agg_check`` (N > 1:
+replica identity + one fused aggregation vs torch's weighted sum), ``simt_fallbacks`` and the tail of the timed
+region.  ``--impl reference`` runs the unmodified reference (``baseline/_ref``, installed by
+``__graft_entry__.build()`` or lazily here) through its own ``run()`` in separate processes.
 """
 
 from __future__ import annotations

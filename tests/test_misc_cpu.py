@@ -382,3 +382,43 @@ def test_vbgmm_active_modes_match_sklearn_on_credit_shape():
     assert outside.max() <= 2, outside.tolist()
     assert (outside == 0).mean() >= 2.0 / 3.0, outside.tolist()
     assert np.mean(dist_med) <= np.mean(spread) + 0.5, (np.mean(dist_med), np.mean(spread))
+
+
+def test_reference_install_and_harness_helpers(tmp_path, monkeypatch):
+    """Reference arm plumbing that must work wherever bench.py runs: the installer copies the reference byte for byte
+    (verified by hash) and the budgeted harness reads per-round times off the per-epoch CSVs."""
+    import sys
+
+    here = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline")
+    sys.path.insert(0, here)
+    try:
+        import install_ref
+        import ref_harness
+    finally:
+        sys.path.remove(here)
+    if os.path.isdir(os.path.join(install_ref.REF_SRC, "Server", "dtds")):
+        assert install_ref.ensure_installed()
+        v = install_ref.verify()
+        assert v["checked"] and v["files"] >= 10 and v["modified_or_missing"] == []
+    # per-epoch CSV marks -> round periods (what a budget-truncated run reports)
+    base = tmp_path / "run"
+    res = base / "server" / "Intrusion_result"
+    res.mkdir(parents=True)
+    for i, t in enumerate((100.0, 130.5, 160.0, 191.0)):
+        f = res / f"Intrusion_synthesis_epoch_{i}.csv"
+        f.write_text("x\n")
+        os.utime(f, (t, t))
+    marks = ref_harness._round_csvs(str(base))
+    assert [m[0] for m in marks] == [0, 1, 2, 3]
+    periods = [b[1] - a[1] for a, b in zip(marks, marks[1:])]
+    assert np.allclose(periods, [30.5, 29.5, 31.0])
+
+
+def test_device_stats_sample_counts_match_reference_formula():
+    """``int(sum_rows * frac_i)`` per client as at ``Server/dtds/distributed.py:732-734`` (float rounding included)."""
+    from fed_tgan_b200.parallel.devstats import sample_counts
+
+    rows = [1000, 3000, 2500, 7]
+    n_total = sum(rows)
+    assert sample_counts(rows) == [int(n_total * (r / n_total)) for r in rows]
+    assert all(abs(a - b) <= 1 for a, b in zip(sample_counts(rows), rows))
