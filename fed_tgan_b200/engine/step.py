@@ -151,6 +151,7 @@ class TrainEngine:
         self.loss_g_adv = torch.zeros(1, **f32)
         self.ce = torch.zeros(1, **f32)
         self.iterations = 0
+        self.dmid_counter = torch.zeros(1, dtype=torch.int32, device=dev)     # last-CTA counter of the fused D middle
 
     # ------------------------------------------------------------------ helpers
     def branch(self, k):
@@ -284,25 +285,47 @@ class TrainEngine:
         self.join(1)
 
     # ------------------------------------------------------------ discriminator
+    def _fused_dmid(self):
+        """Layer 1 + head + both backward signals as ONE row-local fp32 kernel (``ftg_d_mid``): standard two-hidden-
+        layer discriminator on the device with hidden widths <= 512.  Opt-in (``FEDTGAN_FUSED_DMID=1``): it removes two
+        launches per D pass but is not faster than them yet."""
+        if len(self.dhid) != 2 or self.device.type != "cuda" or not ops.native_available() or ops._force_reference():
+            return False
+        from ..ops import native
+
+        return native.d_mid_enabled() and native.d_mid_supported(self.dhid[0], self.dhid[1])
+
     def d_forward(self, rows, inject, key, stream, rowscale=None, loss_out=None, rs_sig=None):
         """Forward rows ``[0:rows)`` of the packed batch; fills Lact/Mask/y, the fused scalar
-        ``loss_out = sum rowscale * y`` and the head's backward signal ``Z_{L-1}``."""
+        ``loss_out = sum rowscale * y`` and the head's backward signal ``Z_{L-1}`` (with the fused middle kernel
+        also ``Z_0``: then ``d_signals`` has nothing left to do)."""
         cfg = self.cfg
         x = self.Xp[:rows]
+        nl = len(self.dhid)
+        fused = self._fused_dmid()
+        self._signals_done = False
         for l, hl in enumerate(self.dhid):
             u = None
             if inject is not None and key in inject:
                 u = inject[key][l]
+            if fused and l == 1:
+                ops.d_mid(x, self._dw(1), self._db(1), self.Lact[1][:rows], self.Mask[1][:rows], self.Mask[0][:rows],
+                          self._dw(nl).view(-1), self._db(nl), self.y[:rows], rowscale, loss_out, rs_sig,
+                          self.Z[1][:rows], self.Z[0][:rows], u=u, rng=self.rng, stream=stream + 1,
+                          slope=cfg.leaky_slope, p=cfg.dropout_p, counter=self.dmid_counter)
+                self._signals_done = True
+                return
             ops.linear(x, self._dw(l), self.Lact[l][:rows], bias=self._db(l), act="leaky_dropout",
                        mask_out=self.Mask[l][:rows], u=u, rng=self.rng, stream=stream + l,
                        slope=cfg.leaky_slope, p=cfg.dropout_p)
             x = self.Lact[l][:rows]
-        nl = len(self.dhid)
         ops.d_head(x, self._dw(nl), self._db(nl), self.y[:rows], rowscale, loss_out, rs_sig,
                    self.Mask[nl - 1][:rows], self.Z[nl - 1][:rows])
 
     def d_signals(self, rows, rowscale):
         """Backward signals ``Z_l = dLoss/d(pre-activation_l)`` for ``loss = sum rowscale*y``."""
+        if getattr(self, "_signals_done", False):
+            return
         nl = len(self.dhid)                 # Z[nl-1] was produced by d_head inside d_forward
         for l in range(nl - 1, 0, -1):
             ops.linear(self.Z[l][:rows], self._dw(l), self.Z[l - 1][:rows], b_t=True, mask_in=self.Mask[l - 1][:rows])

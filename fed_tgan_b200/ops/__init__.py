@@ -22,7 +22,7 @@ from . import reference
 from .reference import RngState  # noqa: F401
 
 _NAMES = [
-    "linear", "linear_bn_relu", "rowdot", "d_head", "colsum", "scale_outer_mask", "bn_relu_fwd", "bn_relu_bwd", "activate_fwd",
+    "linear", "linear_bn_relu", "rowdot", "d_head", "d_mid", "colsum", "scale_outer_mask", "bn_relu_fwd", "bn_relu_bwd", "activate_fwd",
     "activate_bwd", "gen_output_bwd", "cond_loss_fwd_bwd", "slerp", "gp_penalty", "adam_step", "fill_normal",
     "sample_condvec", "write_condvec", "sample_rows", "expand_rows", "argsort_perm",
     "vgm_decode", "vgm_encode",

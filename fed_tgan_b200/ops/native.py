@@ -79,6 +79,9 @@ _gen_out_bwd = _sig("ftg_gen_output_bwd", [_vp, _i, _vp, _i, _i, _i, _vp, _vp, _
 _prep_rows = _sig("ftg_prep_rows", [_i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp, _i, _i, _vp, _i, _vp,
                                     _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _i, _vp, _i, _i, _vp])
 _d_head = _sig("ftg_d_head", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp])
+_d_mid = _sig("ftg_d_mid", [_vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i,
+                            _vp, _i, _vp, _i, _vp, _i, _f, _f, _vp, _vp])
+_d_mid_supported = _sig("ftg_d_mid_supported", [_i, _i])
 _colsum = _sig("ftg_colsum", [_vp, _i, _i, _i, _vp, _vp, _i, _vp])
 _som = _sig("ftg_scale_outer_mask", [_vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp])
 _bn_fwd = _sig("ftg_bn_relu_fwd", [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp])
@@ -341,6 +344,45 @@ def d_head(a, w, bias, y, rs_loss, loss_out, rs_sig, mask, z):
     pz, ldz = _m(z)
     _ck(_d_head(pa, lda, a.shape[0], a.shape[1], _p(w), _p(bias), _p(y), _p(rs_loss), _p(loss_out), _p(rs_sig), pm,
                 ldm, pz, ldz, _stream()), "d_head")
+    return y
+
+
+_dmid_counters = {}
+
+
+def d_mid_supported(h0: int, h1: int) -> bool:
+    """Shape check of the fused discriminator-middle kernel (hidden widths <= 512, H0 % 4 == 0)."""
+    return bool(_d_mid_supported(int(h0), int(h1)))
+
+
+def d_mid_enabled() -> bool:
+    """Opt-in (``FEDTGAN_FUSED_DMID=1``): measured 26-30 us per launch inside the iteration's graph against ~24 us for
+    the three launches it replaces (tcgen05 GEMM + k_d_head + tcgen05 GEMM), see profiles/gemm_cluster_protocols.md."""
+    return os.environ.get("FEDTGAN_FUSED_DMID", "0") == "1"
+
+
+def d_mid(a0, w1, b1, a1, mask1, mask0, w_head, b_head, y, rs_loss, loss_out, rs_sig, z1, z0, *, u=None, rng=None,
+          stream=0, slope=0.2, p=0.5, counter=None):
+    """Discriminator layer 1 + head + backward signals of both in one launch (exact fp32), see ``ftg_d_mid``."""
+    pa0, lda0 = _m(a0)
+    pw, ldw = _m(w1)
+    pa1, lda1 = _m(a1)
+    pm1, ldm1 = _m(mask1)
+    pm0, ldm0 = _m(mask0)
+    pz1, ldz1 = _m(z1)
+    pz0, ldz0 = _m(z0)
+    pu, ldu = _m(u)
+    if counter is None:                      # callers that may overlap on the GPU pass their own counter
+        dev = a0.device.index
+        if dev not in _dmid_counters:
+            _dmid_counters[dev] = torch.zeros(1, dtype=torch.int32, device=a0.device)
+        counter = _dmid_counters[dev]
+    M, H0 = a0.shape
+    H1 = w1.shape[0]
+    _ck(_d_mid(pa0, lda0, M, H0, H1, pw, ldw, _p(b1), pa1, lda1, pm1, ldm1, pm0, ldm0, _p(w_head), _p(b_head), _p(y),
+               _p(rs_loss), _p(loss_out), _p(rs_sig), pz1, ldz1, pz0, ldz0, pu, ldu,
+               _p(rng.state) if rng is not None else None, int(stream), float(slope), float(p),
+               _p(counter), _stream()), "d_mid")
     return y
 
 

@@ -151,6 +151,16 @@ def bn_relu_fwd(a, gamma, beta, running_mean, running_var, out, save_mean, save_
     return out
 
 
+def d_mid(a0, w1, b1, a1, mask1, mask0, w_head, b_head, y, rs_loss, loss_out, rs_sig, z1, z0, *, u=None, rng=None,
+          stream=0, slope=0.2, p=0.5, counter=None):
+    """Layer 1 of the two-hidden-layer discriminator, its head and the backward signals of both (the composition the
+    fused ``ftg_d_mid`` kernel replaces): ``linear(leaky_dropout)`` -> ``d_head`` -> ``linear(b_t, mask_in)``."""
+    linear(a0, w1, a1, bias=b1, act="leaky_dropout", mask_out=mask1, u=u, rng=rng, stream=stream, slope=slope, p=p)
+    d_head(a1, w_head, b_head, y, rs_loss, loss_out, rs_sig, mask1, z1)
+    linear(z1, w1, z0, b_t=True, mask_in=mask0)
+    return y
+
+
 def linear_bn_relu(x, w, a_out, out, *, bias, gamma, beta, running_mean, running_var, save_mean=None, save_invstd=None,
                    eps=1e-5, momentum=0.1, num_batches_tracked=None, precision=None):
     """``a_out = x @ w.T + bias``; ``out = relu(batchnorm_train(a_out))`` (Residual block, ``ctgan.py:40-44``)."""

@@ -116,6 +116,18 @@ int ftg_d_head(const float* a, int lda, int M, int K, const float* w, const floa
                int ldz, ftg_stream_t stream);
 int ftg_colsum(const float* a, int lda, int M, int N, const float* rowscale, float* out, int accumulate,
                ftg_stream_t stream);
+/* Fused middle of the two-hidden-layer PacGAN discriminator for the packed batch, one launch, exact fp32:
+ *   a1 = dropout(leaky(a0 . W1^T + b1)) (+ mask1);  y = a1 . w + b;  loss = sum rs_loss*y;
+ *   Z1 = rs_sig (x) w (.) mask1;  Z0 = (Z1 . W1) (.) mask0
+ * (= Linear+LeakyReLU+Dropout, the head Linear, and their backward signals: S/dtds/synthesizers/ctgan.py:22-30).
+ * Row local (no BatchNorm in D): a CTA owns 4 rows.  Needs H0, H1 <= 512, H0 % 4 == 0 (ftg_d_mid_supported), `counter`
+ * = one zero-initialised device int when loss_out != NULL.  Dropout uniforms as in ftg_gemm_tc's epilogue. */
+int ftg_d_mid_supported(int H0, int H1);
+int ftg_d_mid(const float* a0, int lda0, int M, int H0, int H1, const float* w1, int ldw1, const float* b1, float* a1,
+              int lda1, float* mask1, int ldm1, const float* mask0, int ldm0, const float* w_head, const float* b_head,
+              float* y, const float* rs_loss, float* loss_out, const float* rs_sig, float* z1, int ldz1, float* z0,
+              int ldz0, const float* drop_u, int ldu, const int64_t* rng_state, int rng_stream, float slope,
+              float drop_p, int* counter, ftg_stream_t stream);
 int ftg_scale_outer_mask(const float* rowscale, const float* v, const float* mask, int ldm, float* out,
                          int ldo, int M, int N, ftg_stream_t stream);
 

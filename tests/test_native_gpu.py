@@ -718,3 +718,51 @@ def test_fed_stats_to_weights_vs_scipy(N):
     N.fedavg_local(reps, st.weights, [])
     torch.cuda.synchronize()
     assert torch.allclose(reps[0], want, atol=1e-5) and torch.equal(reps[0], reps[1])
+
+
+@pytest.mark.parametrize("shape", [(150, 256, 256), (50, 256, 256), (7, 64, 32), (33, 512, 100)], ids=lambda s: "x".join(map(str, s)))
+def test_d_mid_fused_vs_composition(N, shape):
+    """Fused discriminator middle (layer 1 + head + both backward signals, one row-local fp32 kernel) vs the
+    composition it replaces: linear(leaky_dropout) -> d_head -> linear(b_t, mask_in)  (reference: Discriminator,
+    ctgan.py:22-30, and its autograd backward)."""
+    M, H0, H1 = shape
+    assert N.d_mid_supported(H0, H1)
+    a0 = padded(M, H0, H0 + 4, 1)
+    w1 = padded(H1, H0, H0 + 8, 2).mul_(0.1)
+    b1, wh, bh = rnd(H1, seed=3) * 0.1, rnd(H1, seed=4), rnd(1, seed=5)
+    mask0 = (uni(M, H0, seed=6) > 0.5).float() * 2.0
+    u = uni(M, H1, seed=7)
+    rs_loss, rs_sig = rnd(M, seed=8), rnd(M, seed=9)
+    out = {}
+    for name, fn in (("native", N.d_mid), ("ref", R.d_mid)):
+        a1, m1 = torch.full((M, H1), 9.0, device=dev()), torch.full((M, H1), 9.0, device=dev())
+        z1, z0 = torch.full((M, H1), 9.0, device=dev()), torch.full((M, H0 + 4), 9.0, device=dev())[:, :H0]
+        y, loss = torch.zeros(M, device=dev()), torch.zeros(1, device=dev())
+        n0 = N.launch_count()
+        fn(a0, w1, b1, a1, m1, mask0, wh, bh, y, rs_loss, loss, rs_sig, z1, z0, u=u, slope=0.2, p=0.5)
+        torch.cuda.synchronize()
+        if name == "native":
+            assert N.launch_count() - n0 == 1
+        out[name] = (a1, m1, y, loss, z1, z0.clone())
+    for i, what in enumerate(("a1", "mask1", "y", "loss", "z1", "z0")):
+        g, r = out["native"][i], out["ref"][i]
+        if what == "mask1":
+            assert (g != r).float().mean().item() < 1e-4, what          # only where the pre-activation rounds across 0
+            continue
+        err = (g.double() - r.double()).abs().max().item()
+        assert err <= 2e-5 * (1.0 + r.abs().max().item()) * (4.0 if what in ("loss", "z0") else 1.0), (what, err)
+    # Philox dropout: same keep rate and value set as the GEMM epilogue, and a second launch re-arms the loss counter
+    rng = R.RngState(3, dev())
+    rng.tick()
+    a1, m1 = torch.empty(M, H1, device=dev()), torch.empty(M, H1, device=dev())
+    z1, z0 = torch.empty(M, H1, device=dev()), torch.empty(M, H0, device=dev())
+    y, loss = torch.zeros(M, device=dev()), torch.zeros(1, device=dev())
+    for _ in range(2):
+        N.d_mid(a0, w1, b1, a1, m1, mask0, wh, bh, y, rs_loss, loss, rs_sig, z1, z0, rng=rng, stream=9)
+    torch.cuda.synchronize()
+    assert abs((m1 != 0).float().mean().item() - 0.5) < 0.06
+    assert abs(loss.item() - float((rs_loss * y).sum())) <= 1e-4 * (1 + abs(loss.item()))
+    ref_mask = torch.empty(M, H1, device=dev())
+    N.linear(a0, w1, torch.empty(M, H1, device=dev()), bias=b1, act="leaky_dropout", mask_out=ref_mask, rng=rng, stream=9,
+             precision="fp32")
+    assert (ref_mask != m1).float().mean().item() < 1e-4        # same Philox draw per element as the GEMM epilogue
