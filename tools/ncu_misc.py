@@ -5,7 +5,7 @@ between cudaProfilerStart/Stop, for `ncu --profile-from-start off`:
   k_fed_finish (fused statistics -> weights), k_distances / k_finish (older host-gathered variant),
   k_fedavg_local, k_fedavg_twoshot / k_fedavg_oneshot (world = 1: same code path incl. flag barriers),
   k_gemm_tc_persist (persistent double-buffered-TMEM GEMM), k_gemm_tc<..., EPI_BN> (fused BatchNorm epilogue, tf32 and
-  fp32x3), k_vgm_encode / k_vgm_decode, k_gemm_simt.
+  fp32x3), k_gemm_simt, k_d_mid.
 """
 import os
 import sys
@@ -48,6 +48,16 @@ g_, b_ = torch.ones(256, device=dev), torch.zeros(256, device=dev)
 rm, rv = torch.zeros(256, device=dev), torch.ones(256, device=dev)
 
 
+from fed_tgan_b200.ops import reference as Rf  # noqa: E402
+
+dm = {"a0": torch.randn(150, 256, device=dev), "w1": torch.randn(256, 256, device=dev) * 0.1,
+      "b1": torch.randn(256, device=dev), "wh": torch.randn(256, device=dev), "bh": torch.randn(1, device=dev),
+      "m0": torch.ones(150, 256, device=dev), "rs": torch.randn(150, device=dev), "y": torch.zeros(150, device=dev),
+      "loss": torch.zeros(1, device=dev), "rng": Rf.RngState(1, dev)}
+for k_ in ("a1", "m1", "z1", "z0"):
+    dm[k_] = torch.empty(150, 256, device=dev)
+
+
 def run(rid):
     cen = N.quantile_centers(x, K)                                   # k_gmm_sample_sort (row-sort mode)
     N.vbgmm_fit(x, cen)                                              # k_vbgmm_fit
@@ -61,6 +71,8 @@ def run(rid):
     for prec in ("tf32", "fp32x3"):                                  # fused BatchNorm epilogue
         N.linear_bn_relu(xb, wb, ab, hb, bias=bias, gamma=g_, beta=b_, running_mean=rm, running_var=rv, precision=prec)
     N.linear(xb, wb, ab, bias=bias, precision="fp32")                # k_gemm_simt
+    N.d_mid(dm["a0"], dm["w1"], dm["b1"], dm["a1"], dm["m1"], dm["m0"], dm["wh"], dm["bh"], dm["y"], dm["rs"], dm["loss"],
+            dm["rs"], dm["z1"], dm["z0"], rng=dm["rng"], stream=3)   # k_d_mid (fused discriminator middle)
 
 
 run(1)
