@@ -8,7 +8,7 @@
 //     Z1 = rs_sig (x) w (.) mask1                   [M, H1]   d loss / d pre-activation of layer 1
 //     Z0 = (Z1 . W1) (.) mask0                      [M, H0]   d loss / d pre-activation of layer 0
 // As three launches (tcgen05 GEMM, k_d_head, tcgen05 GEMM) these cost 22-24 us of dependent-launch latency per
-// step for 6.6 MFLOP.  Here one CTA owns RPB rows and runs the whole chain out of shared memory in exact fp32
+// step for 6.6 MFLOP.  Here one CTA owns DM_RPB rows and runs the whole chain out of shared memory in exact fp32
 // FMA: W1 (256 KB for 256 x 256) is streamed from L2 ONCE per CTA, used both ways (a warp per output for
 // the forward dot products, a thread per input column for the transposed product), through a cp.async ring.  The scalar loss is summed in
 // fixed row order by the last CTA to finish (deterministic).  Used when both hidden widths are <= 512.
@@ -17,8 +17,8 @@
 namespace {
 
 constexpr int DM_THREADS = 256;
-constexpr int DM_RPB = 4;          // rows per CTA
-static_assert(DM_RPB == 4, "the transposed Z1 staging is read as one float4 per n");
+constexpr int DM_RPB = 2;          // rows per CTA (75 / 25 CTAs for the 150- / 50-row packed batches)
+static_assert(DM_RPB == 2, "the transposed Z1 staging is read as one float2 per n");
 constexpr int DM_MAXH = 512;
 constexpr int DM_CH = 32;           // W1 rows per shared-memory chunk
 
@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
   DTL(0);
   FTG_PDL_ENTER();
   DTL(1);
-  extern __shared__ __align__(16) float wbuf[];                 // [2][DM_CH][H0]
+  extern __shared__ __align__(16) float wbuf[];                 // [nbuf][DM_CH][H0]
   __shared__ __align__(16) float a0s[DM_RPB][DM_MAXH];
   __shared__ __align__(16) float a1s[DM_RPB][DM_MAXH];
   __shared__ __align__(16) float z1t[DM_MAXH][DM_RPB];           // Z1 of this CTA's rows, [n][row]: one 16 B broadcast per n
@@ -74,16 +74,19 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
   const int H0 = P.H0, H1 = P.H1;
   const int n_chunks = (H1 + DM_CH - 1) / DM_CH;
   const int row4 = H0 >> 2;                                     // float4 per W1 row
+  // ring depth: a chunk needs ~2 us from L2 (measured: with 2 buffers every chunk waited 4-5 k cycles for its data)
+  const int nbuf = (H0 <= 256) ? 4 : 2;
   auto load_chunk = [&](int c) {
-    float* dst = wbuf + (size_t)(c & 1) * DM_CH * H0;
+    float* dst = wbuf + (size_t)(c % nbuf) * DM_CH * H0;
     const int n0 = c * DM_CH;
-    for (int i = threadIdx.x; i < DM_CH * row4; i += DM_THREADS) {
-      const int n = i / row4, k4 = i - n * row4;
-      if (n0 + n < H1) cp_async16(dst + n * H0 + k4 * 4, P.w1 + (size_t)(n0 + n) * P.ldw1 + k4 * 4);
-    }
-    cp_async_commit();
+    if (c < n_chunks)
+      for (int i = threadIdx.x; i < DM_CH * row4; i += DM_THREADS) {
+        const int n = i / row4, k4 = i - n * row4;
+        if (n0 + n < H1) cp_async16(dst + n * H0 + k4 * 4, P.w1 + (size_t)(n0 + n) * P.ldw1 + k4 * 4);
+      }
+    cp_async_commit();                                          // (an empty group past the end keeps the count uniform)
   };
-  load_chunk(0);
+  for (int c = 0; c < nbuf - 1; ++c) load_chunk(c);
   for (int e = threadIdx.x; e < DM_RPB * H0; e += DM_THREADS) {
     const int r = e / H0, k = e - r * H0, m = m_base + r;
     a0s[r][k] = m < P.M ? P.a0[(size_t)m * P.lda0 + k] : 0.f;
@@ -106,11 +109,12 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
 #pragma unroll
     for (int r = 0; r < DM_RPB; ++r) zacc[j][r] = 0.f;
   for (int c = 0; c < n_chunks; ++c) {
-    if (c + 1 < n_chunks) { load_chunk(c + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    load_chunk(c + nbuf - 1);                                   // refills the buffer chunk c - 1 has just released
+    if (nbuf == 4) cp_async_wait<3>(); else cp_async_wait<1>();
     __syncthreads();                                            // chunk c (and, first time, a0s) visible to all
     if (c == 0) DTL(2);
     if (c == 1) DTL(3);
-    const float* wc = wbuf + (size_t)(c & 1) * DM_CH * H0;
+    const float* wc = wbuf + (size_t)(c % nbuf) * DM_CH * H0;
     const int n0 = c * DM_CH;
     // ---- forward: a warp owns DM_CH / 8 = 4 outputs n of the chunk; all operands come from shared memory
     // (b1, w_head, the dropout uniforms and the row scales were staged up front: a global load per output in
@@ -183,13 +187,12 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
 #pragma unroll 8
         for (int nl = 0; nl < n_hi; ++nl) {
           const float w = wc[nl * H0 + k];
-          const float4 z = *reinterpret_cast<const float4*>(&z1t[n0 + nl][0]);
+          const float2 z = *reinterpret_cast<const float2*>(&z1t[n0 + nl][0]);
           zacc[j][0] = fmaf(z.x, w, zacc[j][0]); zacc[j][1] = fmaf(z.y, w, zacc[j][1]);
-          zacc[j][2] = fmaf(z.z, w, zacc[j][2]); zacc[j][3] = fmaf(z.w, w, zacc[j][3]);
         }
       }
     }
-    __syncthreads();                                            // buffer (c & 1) may be refilled by chunk c + 2
+    __syncthreads();                                            // this chunk's buffer may be refilled now
   }
   DTL(4);
   // ---- head: y[m] = a1[m,:] . w + b   (warp r owns row r)
@@ -260,7 +263,7 @@ extern "C" int ftg_d_mid(const float* a0, int lda0, int M, int H0, int H1, const
   P.rs_sig = rs_sig; P.z1 = z1; P.ldz1 = ldz1; P.z0 = z0; P.ldz0 = ldz0; P.drop_u = drop_u; P.ldu = ldu;
   P.rng_state = rng_state; P.rng_stream = rng_stream; P.slope = slope; P.drop_p = drop_p; P.M = M; P.H0 = H0; P.H1 = H1;
   P.counter = counter;
-  const size_t dyn = (size_t)2 * DM_CH * H0 * sizeof(float);
+  const size_t dyn = (size_t)(H0 <= 256 ? 4 : 2) * DM_CH * H0 * sizeof(float);
   static std::atomic<bool> attr_done[64];
   int dev_id = 0;
   if (cudaGetDevice(&dev_id) != cudaSuccess || dev_id < 0 || dev_id >= 64) return FTG_ERR_UNSUPPORTED;
