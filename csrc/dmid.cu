@@ -16,7 +16,7 @@
 
 namespace {
 
-constexpr int DM_THREADS = 256;
+constexpr int DM_THREADS = 512;     // 16 warps: the chain is instruction-latency bound, 4 warps per scheduler hide it
 constexpr int DM_RPB = 2;          // rows per CTA (75 / 25 CTAs for the 150- / 50-row packed batches)
 static_assert(DM_RPB == 2, "the transposed Z1 staging is read as one float2 per n");
 constexpr int DM_MAXH = 512;
@@ -76,14 +76,24 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
   const int row4 = H0 >> 2;                                     // float4 per W1 row
   // ring depth: a chunk needs ~2 us from L2 (measured: with 2 buffers every chunk waited 4-5 k cycles for its data)
   const int nbuf = (H0 <= 256) ? 4 : 2;
+  // per-thread copy pattern of a chunk (identical for every chunk: only the base row moves)
+  constexpr int CPT = (DM_CH * (DM_MAXH / 4) + DM_THREADS - 1) / DM_THREADS;     // float4 copies per thread, worst case
+  int cp_n[CPT], cp_k[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) {
+    const int i = threadIdx.x + j * DM_THREADS;
+    cp_n[j] = i < DM_CH * row4 ? i / row4 : -1;
+    cp_k[j] = (i - (i / row4) * row4) * 4;
+  }
   auto load_chunk = [&](int c) {
     float* dst = wbuf + (size_t)(c % nbuf) * DM_CH * H0;
     const int n0 = c * DM_CH;
-    if (c < n_chunks)
-      for (int i = threadIdx.x; i < DM_CH * row4; i += DM_THREADS) {
-        const int n = i / row4, k4 = i - n * row4;
-        if (n0 + n < H1) cp_async16(dst + n * H0 + k4 * 4, P.w1 + (size_t)(n0 + n) * P.ldw1 + k4 * 4);
-      }
+    if (c < n_chunks) {
+#pragma unroll
+      for (int j = 0; j < CPT; ++j)
+        if (cp_n[j] >= 0 && n0 + cp_n[j] < H1)
+          cp_async16(dst + cp_n[j] * H0 + cp_k[j], P.w1 + (size_t)(n0 + cp_n[j]) * P.ldw1 + cp_k[j]);
+    }
     cp_async_commit();                                          // (an empty group past the end keeps the count uniform)
   };
   for (int c = 0; c < nbuf - 1; ++c) load_chunk(c);
@@ -103,7 +113,7 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
   if (threadIdx.x < DM_RPB) rss[threadIdx.x] = (m_base + threadIdx.x < P.M) ? P.rs_sig[m_base + threadIdx.x] : 0.f;
   const uint64_t seed = P.rng_state ? (uint64_t)P.rng_state[0] : 0ull, step = P.rng_state ? (uint64_t)P.rng_state[1] : 0ull;
   const float keep_scale = 1.f / (1.f - P.drop_p);
-  float zacc[2][DM_RPB];                                        // Z0 accumulators: k = tid and tid + 256
+  float zacc[2][DM_RPB];                                        // partial Z0: k = (tid & 255) and + 256, this half's rows
 #pragma unroll
   for (int j = 0; j < 2; ++j)
 #pragma unroll
@@ -177,18 +187,25 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
         }
       }
     }
+    if (c == 0) DTL(6);
     __syncthreads();                                            // Z1[., n0 .. n0+CH) of this CTA's rows are in z1s
-    // ---- transposed accumulation on the same chunk: a thread per input column k
-    const int n_hi = min(DM_CH, H1 - n0);
+    if (c == 0) DTL(7);
+    // ---- transposed accumulation on the same chunk: thread (k, half) covers half of the chunk's rows for input
+    // column k (and k + 256 when H0 > 256); the two halves are combined once, after the last chunk
+    {
+      const int n_hi = min(DM_CH, H1 - n0);
+      const int half = threadIdx.x >> 8, kk = threadIdx.x & 255;
+      const int nl0 = half * (DM_CH / 2), nl1 = min(n_hi, nl0 + DM_CH / 2);
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int k = threadIdx.x + j * DM_THREADS;
-      if (k < H0) {
+      for (int j = 0; j < 2; ++j) {
+        const int k = kk + j * 256;
+        if (k < H0) {
 #pragma unroll 8
-        for (int nl = 0; nl < n_hi; ++nl) {
-          const float w = wc[nl * H0 + k];
-          const float2 z = *reinterpret_cast<const float2*>(&z1t[n0 + nl][0]);
-          zacc[j][0] = fmaf(z.x, w, zacc[j][0]); zacc[j][1] = fmaf(z.y, w, zacc[j][1]);
+          for (int nl = nl0; nl < nl1; ++nl) {
+            const float w = wc[nl * H0 + k];
+            const float2 z = *reinterpret_cast<const float2*>(&z1t[n0 + nl][0]);
+            zacc[j][0] = fmaf(z.x, w, zacc[j][0]); zacc[j][1] = fmaf(z.y, w, zacc[j][1]);
+          }
         }
       }
     }
@@ -203,14 +220,26 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
     s = warp_sum(s);
     if (lane == 0 && m < P.M) P.y[m] = s + (P.b_head ? P.b_head[0] : 0.f);
   }
+  // combine the two halves' partial Z0 through shared memory (a0s is free now), apply mask0, store
+  {
+    const int half = threadIdx.x >> 8, kk = threadIdx.x & 255;
+    if (half == 1) {
 #pragma unroll
-  for (int j = 0; j < 2; ++j) {
-    const int k = threadIdx.x + j * DM_THREADS;
-    if (k < H0) {
+      for (int j = 0; j < 2; ++j)
+        if (kk + j * 256 < H0) { a0s[0][kk + j * 256] = zacc[j][0]; a0s[1][kk + j * 256] = zacc[j][1]; }
+    }
+    __syncthreads();
+    if (half == 0) {
 #pragma unroll
-      for (int r = 0; r < DM_RPB; ++r) {
-        const int m = m_base + r;
-        if (m < P.M) P.z0[(size_t)m * P.ldz0 + k] = zacc[j][r] * P.mask0[(size_t)m * P.ldm0 + k];
+      for (int j = 0; j < 2; ++j) {
+        const int k = kk + j * 256;
+        if (k < H0) {
+#pragma unroll
+          for (int r = 0; r < DM_RPB; ++r) {
+            const int m = m_base + r;
+            if (m < P.M) P.z0[(size_t)m * P.ldz0 + k] = (zacc[j][r] + a0s[r][k]) * P.mask0[(size_t)m * P.ldm0 + k];
+          }
+        }
       }
     }
   }
@@ -231,7 +260,6 @@ __global__ void __launch_bounds__(DM_THREADS) k_d_mid(const DMidArgs P) {
   for (int m = threadIdx.x; m < P.M; m += DM_THREADS) cs += P.rs_loss[m] * __ldcg(P.y + m);
   const float tot = block_sum(cs, red);
   if (threadIdx.x == 0) P.loss_out[0] = tot;
-  DTL(6);
 }
 
 }  // namespace

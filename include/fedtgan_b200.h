@@ -120,7 +120,7 @@ int ftg_colsum(const float* a, int lda, int M, int N, const float* rowscale, flo
  *   a1 = dropout(leaky(a0 . W1^T + b1)) (+ mask1);  y = a1 . w + b;  loss = sum rs_loss*y;
  *   Z1 = rs_sig (x) w (.) mask1;  Z0 = (Z1 . W1) (.) mask0
  * (= Linear+LeakyReLU+Dropout, the head Linear, and their backward signals: S/dtds/synthesizers/ctgan.py:22-30).
- * Row local (no BatchNorm in D): a CTA owns 2 rows and streams W1 once through a cp.async ring.  Needs H0, H1 <= 512, H0 % 4 == 0 (ftg_d_mid_supported), `counter`
+ * Row local (no BatchNorm in D): a CTA of 16 warps owns 2 rows and streams W1 once through a cp.async ring.  Needs H0, H1 <= 512, H0 % 4 == 0 (ftg_d_mid_supported), `counter`
  * = one zero-initialised device int when loss_out != NULL.  Dropout uniforms as in ftg_gemm_tc's epilogue. */
 int ftg_d_mid_supported(int H0, int H1);
 int ftg_d_mid(const float* a0, int lda0, int M, int H0, int H1, const float* w1, int ldw1, const float* b1, float* a1,

@@ -32,7 +32,7 @@ for M in (150, 50):
     buf = (C.c_longlong * 8)()
     lib.ftg_d_mid_timeline(0, buf)
     t = list(buf)
-    names = ["entry", "after_pdl_wait", "chunk0_ready", "chunk1_ready", "chunks_done", "stores_done", "loss_done"]
+    names = ["entry", "after_pdl_wait", "chunk0_ready", "chunk1_ready", "chunks_done", "stores_done", "chunk0_forward_done_thread0", "chunk0_forward_all_warps"]
     print(M, {n: t[i] - t[0] for i, n in enumerate(names)})
     g = torch.cuda.CUDAGraph()
     s = torch.cuda.Stream()
