@@ -45,6 +45,23 @@ def build(force=False, verbose=False):
     if not force and not _stale():
         return LIB
     os.makedirs(OUT_DIR, exist_ok=True)
+    # One builder at a time: under torchrun every rank imports ops.native at once, and a snapshot copy of the
+    # repo can make the shipped .so look older than the sources.  The first rank builds, the others wait for the
+    # lock and then find a fresh library.
+    import fcntl
+
+    lock = open(os.path.join(OUT_DIR, ".build.lock"), "w")
+    fcntl.flock(lock, fcntl.LOCK_EX)
+    try:
+        if not force and not _stale():
+            return LIB
+        return _build_locked(verbose)
+    finally:
+        fcntl.flock(lock, fcntl.LOCK_UN)
+        lock.close()
+
+
+def _build_locked(verbose=False):
     obj_dir = os.path.join(OUT_DIR, "obj")
     os.makedirs(obj_dir, exist_ok=True)
     cu, cpp = sources()
