@@ -32,12 +32,32 @@ def sources():
     return cu, cpp
 
 
+HASH_FILE = LIB + ".srchash"
+
+
+def _source_hash():
+    """SHA-256 over the contents of every source that goes into the library (names included)."""
+    import hashlib
+
+    h = hashlib.sha256()
+    deps = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC)) + [os.path.join(ROOT, "include", "fedtgan_b200.h")]
+    for d in deps:
+        h.update(os.path.basename(d).encode())
+        with open(d, "rb") as fh:
+            h.update(fh.read())
+    h.update(" ".join(ARCH + NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
 def _stale():
-    if not os.path.exists(LIB):
+    """The shipped library is reused iff it was built from exactly these sources.  (Contents, not mtimes: copying
+    the repo to another machine must not trigger a 1-2 minute rebuild in every test run.)"""
+    if not os.path.exists(LIB) or not os.path.exists(HASH_FILE):
         return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(ROOT, "include", "fedtgan_b200.h")]
-    return any(os.path.getmtime(d) > t for d in deps)
+    try:
+        return open(HASH_FILE).read().strip() != _source_hash()
+    except OSError:
+        return True
 
 
 def build(force=False, verbose=False):
@@ -90,6 +110,9 @@ def _build_locked(verbose=False):
     if res.returncode != 0:
         raise RuntimeError(f"link failed: {res.stdout}")
     os.replace(LIB + ".tmp", LIB)
+    with open(HASH_FILE + ".tmp", "w") as fh:
+        fh.write(_source_hash())
+    os.replace(HASH_FILE + ".tmp", HASH_FILE)
     return LIB
 
 
